@@ -1,0 +1,236 @@
+/* srt.h — C ABI of the B200-native path-tracing device ("libsrt_b200.so").
+ *
+ * This is the drop-in boundary for ONE path of swishersnaaake/sexy-raytracer: the per-pixel
+ * path-tracing loop (reference main.cpp:200-227 -> camera.h:40-50 -> main.cpp:33-52 -> bvh.h:97-105
+ * -> aabb.h:11-27 / model.h:104-181 / sphere.h:54-83 -> material.h:91-245 -> texture.h:26-148
+ * -> color.h:25-41).
+ *
+ * The reference has no FFI; the only device boundary it ever sketched is the per-frame one of
+ * gl.h:28-31
+ *     bool glDevice::init(int w, int h, std::vector<hittableIndexed>&);
+ *     bool glDevice::rtFrame(void* frameData, int w, int h, std::vector<hittableIndexed>&);
+ *     void glDevice::terminate();
+ * fed by hittableVector::build (hittablevector.h:27-31, main.cpp:148-149) and wrapped around the pixel
+ * loop (main.cpp:190-199,228-232).  The entry points below have that shape (hand a flattened scene
+ * over once, then ask for frames), with the 160-byte hittableIndexed record (hittableindexed.h:24-38)
+ * replaced by SoA arrays + 32-byte BVH nodes in the same pre-order (bvh.h:112-148).
+ *
+ * Conventions: plain C structs, plain pointers and sizes, int status codes (0 = OK), no exceptions
+ * cross the boundary.  The caller owns every host pointer; the library owns all device memory.
+ * Calls block and are not re-entrant per srt_device (the reference is single threaded).
+ * Pointers named *_dev are device pointers on the srt_device's GPU; everything else is host memory.
+ * There is no CPU fallback: every compute entry point fails with SRT_ERR_CUDA when no GPU is present.
+ */
+#ifndef SRT_H_
+#define SRT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRT_ABI_VERSION 1
+
+typedef int srt_status;
+enum {
+  SRT_OK = 0,
+  SRT_ERR_INVALID = 1,      /* bad argument / malformed scene description            */
+  SRT_ERR_CUDA = 2,         /* CUDA runtime error (srt_last_error() has the text)     */
+  SRT_ERR_UNSUPPORTED = 3,  /* valid but outside what the device implements           */
+  SRT_ERR_NOMEM = 4
+};
+
+/* ---- primitives ------------------------------------------------------------------------------
+ * Primitive ids are global: triangles first [0, n_tri), then spheres [n_tri, n_tri + n_sph)
+ * (main.cpp:82-86 adds the mesh triangles, main.cpp:90,127,140,144 the spheres).               */
+
+/* One BVH node, 32 bytes, array in the pre-order of bvhNode::populateVector (bvh.h:112-148):
+ * a node's index is assigned before its children, left subtree first.
+ * child >= 0 : index of an inner node;  child < 0 : leaf, primitive id = ~child.
+ * right == SRT_BVH_NONE : the reference's span-1 node (left == right, bvh.h:67-69) - its leaf is
+ * visited once (the second visit of the reference cannot change the record).                  */
+typedef struct srt_bvh_node {
+  float   bmin[3];
+  float   bmax[3];
+  int32_t left;
+  int32_t right;
+} srt_bvh_node;
+#define SRT_BVH_NONE INT32_MIN
+
+/* ---- textures (texture.h) ------------------------------------------------------------------- */
+enum {
+  SRT_TEX_SOLID = 0,    /* solidColor (texture.h:18-32): value = color                          */
+  SRT_TEX_CHECKER = 1,  /* checker (texture.h:34-52): sinf(10x)sinf(10y)sinf(10z) < 0 ? odd : even, x255 */
+  SRT_TEX_IMAGE = 2     /* imagePNG / image3bpp (texture.h:54-154): nearest texel, 0..255 floats */
+};
+typedef struct srt_texture {
+  int32_t        kind;
+  float          color[3];     /* SOLID                                                         */
+  int32_t        even, odd;    /* CHECKER: texture ids (must be SOLID or IMAGE)                 */
+  int32_t        width, height, bpp;  /* IMAGE: bpp = bytes per texel as passed to imagePNG     */
+  const uint8_t* data;         /* IMAGE: height*width*bpp bytes, row 0 first; NULL = the file
+                                  was missing -> value() = (1,0,1) (texture.h:130-131)          */
+} srt_texture;
+
+/* ---- materials (material.h) ----------------------------------------------------------------- */
+enum {
+  SRT_MAT_PBR = 0,         /* pbrMetallicRoughness (material.h:23-85,156-245)                   */
+  SRT_MAT_METAL = 1,       /* metal (material.h:87-102)                                         */
+  SRT_MAT_DIELECTRIC = 2,  /* dielectric (material.h:104-137)                                   */
+  SRT_MAT_LIGHT = 3        /* diffuseLight (material.h:139-154)                                 */
+};
+typedef struct srt_material {
+  int32_t kind;
+  int32_t albedo_tex;     /* PBR albedoMap / LIGHT emit texture; -1 = none                      */
+  int32_t normal_tex;     /* PBR normalMap;    -1 = none                                        */
+  int32_t metallic_tex;   /* PBR metallicMap;  -1 = none                                        */
+  int32_t roughness_tex;  /* PBR roughnessMap; -1 = none (metallicRoughnessMap is never sampled
+                             by the reference, material.h:78, so it has no slot)                */
+  float   albedo[4];      /* PBR albedo factor (vec4f) / METAL albedo (rgb)                     */
+  float   metalness;      /* PBR scalar used when metallic_tex < 0                              */
+  float   roughness;      /* PBR scalar used when roughness_tex < 0                             */
+  float   fuzz;           /* METAL (already clamped to <= 1, material.h:89)                     */
+  float   ir;             /* DIELECTRIC index of refraction                                     */
+} srt_material;
+
+/* ---- scene ---------------------------------------------------------------------------------- */
+typedef struct srt_scene_desc {
+  /* triangles: SoA, 3 floats per vertex position, 2 floats per vertex uv (model.h:71-72 resolved
+     through the uint16 indices of model.h:46)                                                  */
+  int64_t        n_tri;
+  const float*   tri_v0;   /* [n_tri*3] */
+  const float*   tri_v1;
+  const float*   tri_v2;
+  const float*   tri_uv0;  /* [n_tri*2] */
+  const float*   tri_uv1;
+  const float*   tri_uv2;
+  const int32_t* tri_mat;  /* [n_tri]   */
+  /* spheres (sphere.h:40-44) */
+  int64_t        n_sph;
+  const float*   sph_c0;   /* [n_sph*3] center0 */
+  const float*   sph_c1;   /* [n_sph*3] center1 */
+  const float*   sph_t0;   /* [n_sph]   */
+  const float*   sph_t1;   /* [n_sph]   */
+  const float*   sph_r;    /* [n_sph]   */
+  const int32_t* sph_mat;  /* [n_sph]   */
+  /* BVH: root is node 0 */
+  int64_t             n_nodes;
+  const srt_bvh_node* nodes;
+  /* tables */
+  int32_t             n_mat;
+  const srt_material* materials;
+  int32_t             n_tex;
+  const srt_texture*  textures;
+} srt_scene_desc;
+
+/* camera: the ten derived members of camera.h:52-62 (private there; the host class exposes them) */
+typedef struct srt_camera {
+  float origin[3];
+  float lleft[3];
+  float horizontal[3];
+  float vertical[3];
+  float w[3];
+  float hor[3];
+  float vert[3];
+  float lens_radius;
+  float t0, t1;
+} srt_camera;
+
+/* ray.h:6-23 */
+typedef struct srt_ray {
+  float o[3];
+  float dir[3];
+  float time;
+} srt_ray;
+
+/* hitRecord (hittable.h:9-22) + the primitive id the reference does not keep */
+typedef struct srt_hit {
+  int32_t prim;        /* -1 = miss                                                             */
+  int32_t mat;
+  int32_t front_face;
+  float   t;
+  float   p[3];
+  float   normal[3];   /* face-forwarded (hittable.h:18-21)                                     */
+  float   tangent[3];
+  float   bitangent[3];
+  float   uv[2];
+} srt_hit;
+
+typedef struct srt_render_params {
+  int32_t  width, height;
+  int32_t  spp;            /* numSamples of the whole frame (main.cpp:178): the divisor of resolve */
+  int32_t  sample_begin;   /* this call renders global samples [sample_begin, sample_begin+sample_count) */
+  int32_t  sample_count;   /* of every pixel (spp split across GPUs); 0 = all spp      */
+  int32_t  max_bounce;     /* main.cpp:180                                                       */
+  float    background[3];  /* main.cpp:170                                                       */
+  uint64_t seed;           /* Philox key                                                         */
+  int32_t  rr_begin;       /* Russian roulette from this bounce on; 0 = off (the reference has none) */
+  int32_t  variant;        /* 0 = auto, 1 = megakernel, 2 = wavefront                            */
+} srt_render_params;
+
+typedef struct srt_stats {
+  uint64_t paths;
+  uint64_t segments;       /* world.hit calls, main.cpp:39                                       */
+  uint64_t node_visits;    /* aabb::hit calls (only when counters are enabled)                   */
+  uint64_t leaf_tests;     /* triangle::hit + sphere::hit calls (only when counters are enabled) */
+  float    kernel_ms;      /* device time of the render kernel(s), CUDA events on the launch stream */
+  int32_t  launches;       /* kernels launched by the call                                       */
+} srt_stats;
+
+typedef struct srt_device srt_device;
+typedef struct srt_scene  srt_scene;
+
+/* ---- life cycle: replaces glDevice::init / terminate (gl.h:28,31) ----------------------------- */
+srt_status  srt_device_create(int gpu_id, srt_device** out);
+void        srt_device_destroy(srt_device* dev);
+/* copies the flattened scene to the GPU (glDevice::init's SSBO upload, gl.h:252-256)            */
+srt_status  srt_scene_create(srt_device* dev, const srt_scene_desc* desc, srt_scene** out);
+void        srt_scene_destroy(srt_scene* scene);
+int64_t     srt_scene_device_bytes(const srt_scene* scene);
+
+/* ---- parity gate: hittableList::hit on explicit rays (hittablelist.h:33-47 -> bvh.h:97-105) -- */
+srt_status  srt_trace_rays(srt_scene* scene, const srt_ray* rays, int64_t n, float t_min, float t_max,
+                           srt_hit* out_hits);
+
+/* ---- one frame: replaces glDevice::rtFrame + the loop main.cpp:200-227 ------------------------
+ * out_sum_rgb  (optional) [H*W*3] float: sum over this call's samples of rayColor, row 0 = top
+ * out_rgba8    (optional) [H*W*4] writeColorTarget output (color.h:25-41), only meaningful when this
+ *              call rendered all spp samples                                                    */
+srt_status  srt_render(srt_scene* scene, const srt_camera* cam, const srt_render_params* params,
+                       float* out_sum_rgb, uint8_t* out_rgba8, srt_stats* stats);
+
+/* device-resident variants for the multi-GPU path (one process per GPU, NCCL reduce outside):
+ * accumulate ADDS this call's samples into accum_dev [H*W*3] float (caller zeroes it);
+ * resolve applies color.h:25-41 to a summed buffer.                                            */
+srt_status  srt_render_accumulate(srt_scene* scene, const srt_camera* cam, const srt_render_params* params,
+                                  float* accum_dev, srt_stats* stats);
+srt_status  srt_resolve(srt_device* dev, const float* sum_dev, int32_t width, int32_t height, int32_t spp,
+                        uint8_t* rgba8_dev);
+
+/* ---- per-function known-answer entry points (random numbers injected) ------------------------ */
+/* material::scatter + emitted for n (ray, hit) pairs; xi[n*4] are the uniform [0,1) numbers the
+ * sampler consumes ("random numbers").  out_scattered[i] = 0/1 return of scatter. */
+srt_status  srt_shade_kat(srt_scene* scene, const srt_ray* rays_in, const srt_hit* hits, const float* xi,
+                          int64_t n, float* out_attenuation /*n*3*/, float* out_emitted /*n*3*/,
+                          srt_ray* out_rays, int32_t* out_scattered);
+/* texture::value for n lookups: uvp[n*5] = (u, v, p.x, p.y, p.z)                                */
+srt_status  srt_texture_kat(srt_scene* scene, int32_t tex, const float* uvp, int64_t n, float* out_rgb);
+/* camera::getRay + the pixel jitter of main.cpp:210-211 for explicit (pixel, sample) pairs      */
+srt_status  srt_raygen_kat(srt_device* dev, const srt_camera* cam, const srt_render_params* params,
+                           const int32_t* pixel_xy /*n*2*/, const int32_t* sample /*n*/, int64_t n,
+                           srt_ray* out_rays);
+
+/* ---- misc ----------------------------------------------------------------------------------- */
+int         srt_abi_version(void);
+const char* srt_status_string(srt_status s);
+const char* srt_last_error(void);
+/* 1 = count node visits / leaf tests in srt_stats (slower kernels); default 0                   */
+srt_status  srt_set_counters(srt_device* dev, int enabled);
+/* the CUDA stream the device launches on (cudaStream_t as void*), for event timing outside      */
+void*       srt_device_stream(srt_device* dev);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRT_H_ */
