@@ -216,10 +216,14 @@ srt_status  srt_shade_kat(srt_scene* scene, const srt_ray* rays_in, const srt_hi
                           srt_ray* out_rays, int32_t* out_scattered);
 /* texture::value for n lookups: uvp[n*5] = (u, v, p.x, p.y, p.z)                                */
 srt_status  srt_texture_kat(srt_scene* scene, int32_t tex, const float* uvp, int64_t n, float* out_rgb);
-/* camera::getRay + the pixel jitter of main.cpp:210-211 for explicit (pixel, sample) pairs      */
-srt_status  srt_raygen_kat(srt_device* dev, const srt_camera* cam, const srt_render_params* params,
-                           const int32_t* pixel_xy /*n*2*/, const int32_t* sample /*n*/, int64_t n,
-                           srt_ray* out_rays);
+/* camera::getRay (camera.h:40-50) with its random inputs supplied: in[n*5] = (s, t, disk.x, disk.y,
+ * xi_time), disk = the randomInUnitDisk point, xi_time = the uniform number behind randomFloat(t0,t1) */
+srt_status  srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* in, int64_t n, srt_ray* out_rays);
+/* the primary ray the renderer generates for explicit (pixel, sample) pairs: Philox blocks 0 and 1,
+ * the pixel jitter of main.cpp:210-211, then camera::getRay                                      */
+srt_status  srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_render_params* params,
+                             const int32_t* pixel_xy /*n*2*/, const int32_t* sample /*n*/, int64_t n,
+                             srt_ray* out_rays);
 
 /* ---- misc ----------------------------------------------------------------------------------- */
 int         srt_abi_version(void);
@@ -227,6 +231,8 @@ const char* srt_status_string(srt_status s);
 const char* srt_last_error(void);
 /* 1 = count node visits / leaf tests in srt_stats (slower kernels); default 0                   */
 srt_status  srt_set_counters(srt_device* dev, int enabled);
+/* node visits, leaf tests and exact (unfiltered) box tests of the last trace/render call          */
+srt_status  srt_last_counters(srt_device* dev, uint64_t* out3);
 /* the CUDA stream the device launches on (cudaStream_t as void*), for event timing outside      */
 void*       srt_device_stream(srt_device* dev);
 

@@ -95,7 +95,9 @@ PROTOTYPES = {
     "srt_resolve": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_int32, _vp]),
     "srt_shade_kat": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp]),
     "srt_texture_kat": (C.c_int, [_vp, C.c_int32, _vp, C.c_int64, _vp]),
-    "srt_raygen_kat": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.c_int64, _vp]),
+    "srt_getray_kat": (C.c_int, [_vp, C.POINTER(Camera), _vp, C.c_int64, _vp]),
+    "srt_primary_rays": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.c_int64, _vp]),
+    "srt_last_counters": (C.c_int, [_vp, _vp]),
     "srt_abi_version": (C.c_int, []),
     "srt_status_string": (C.c_char_p, [C.c_int]),
     "srt_last_error": (C.c_char_p, []),

@@ -1,0 +1,336 @@
+// srt_b200.cu — host side of the C ABI (include/srt.h) + kernel launches.  Built into libsrt_b200.so:
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false ...   (see build.py)
+// No torch types, no CPU fallback: every compute entry point needs a CUDA device.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "srt_kernels.cuh"
+
+using namespace srt;
+
+static thread_local std::string g_err;
+
+static srt_status fail(srt_status s, const std::string& msg) { g_err = msg; return s; }
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      cudaGetLastError();                                                                          \
+      return fail(SRT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
+    }                                                                                              \
+  } while (0)
+
+struct srt_device {
+  int gpu = 0;
+  int sm_count = 0;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  unsigned long long* d_counters = nullptr;   // 8 x u64, see k_render_mega
+  int counters = 0;
+};
+
+struct srt_scene {
+  srt_device* dev = nullptr;
+  Scene sc{};
+  std::vector<cudaArray_t> arrays;
+  std::vector<cudaTextureObject_t> texobjs;
+  std::vector<void*> buffers;
+  int64_t bytes = 0;
+  int nodes_in_smem = 0;
+  size_t node_bytes = 0;
+};
+
+extern "C" {
+
+int srt_abi_version(void) { return SRT_ABI_VERSION; }
+const char* srt_last_error(void) { return g_err.c_str(); }
+const char* srt_status_string(srt_status s) {
+  switch (s) {
+    case SRT_OK: return "ok";
+    case SRT_ERR_INVALID: return "invalid argument or scene description";
+    case SRT_ERR_CUDA: return "CUDA error";
+    case SRT_ERR_UNSUPPORTED: return "unsupported";
+    case SRT_ERR_NOMEM: return "out of memory";
+    default: return "unknown status";
+  }
+}
+
+srt_status srt_device_create(int gpu_id, srt_device** out) {
+  if (!out) return fail(SRT_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  int n = 0;
+  CK(cudaGetDeviceCount(&n));
+  if (gpu_id < 0 || gpu_id >= n) return fail(SRT_ERR_INVALID, "gpu_id out of range");
+  CK(cudaSetDevice(gpu_id));
+  srt_device* d = new srt_device;
+  d->gpu = gpu_id;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, gpu_id));
+  d->sm_count = prop.multiProcessorCount;
+  d->smem_optin = prop.sharedMemPerBlockOptin;
+  CK(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&d->ev0));
+  CK(cudaEventCreate(&d->ev1));
+  CK(cudaMalloc(&d->d_counters, 8 * sizeof(unsigned long long)));
+  *out = d;
+  return SRT_OK;
+}
+
+void srt_device_destroy(srt_device* d) {
+  if (!d) return;
+  cudaSetDevice(d->gpu);
+  if (d->d_counters) cudaFree(d->d_counters);
+  if (d->ev0) cudaEventDestroy(d->ev0);
+  if (d->ev1) cudaEventDestroy(d->ev1);
+  if (d->stream) cudaStreamDestroy(d->stream);
+  delete d;
+}
+
+srt_status srt_set_counters(srt_device* d, int enabled) {
+  if (!d) return fail(SRT_ERR_INVALID, "device is NULL");
+  d->counters = enabled ? 1 : 0;
+  return SRT_OK;
+}
+void* srt_device_stream(srt_device* d) { return d ? (void*)d->stream : nullptr; }
+
+}  // extern "C"
+
+// ---- scene upload ---------------------------------------------------------------------------------
+static inline float i2f(int32_t v) { float f; memcpy(&f, &v, 4); return f; }
+
+// Threads the caller's tree (srt_bvh_node, root 0) into the skip-link form of srt_core.cuh.
+static srt_status thread_bvh(const srt_scene_desc* d, std::vector<Node>& out, bool& filter_ok) {
+  const int64_t n = d->n_nodes, n_prim = d->n_tri + d->n_sph;
+  out.clear();
+  filter_ok = true;
+  if (n == 0) return SRT_OK;
+  std::vector<uint8_t> seen((size_t)n, 0);
+  struct Frame { int32_t node; int stage; int32_t out_idx; };
+  std::vector<Frame> st;
+  auto leaf_prim = [&](int32_t child, int32_t& prim) -> bool { prim = ~child; return prim >= 0 && prim < n_prim; };
+  auto push_node = [&](int32_t i) -> srt_status {
+    if (i < 0 || i >= n) return fail(SRT_ERR_INVALID, "BVH child index out of range");
+    if (seen[i]) return fail(SRT_ERR_INVALID, "BVH node reachable twice (not a tree)");
+    seen[i] = 1;
+    const srt_bvh_node& s = d->nodes[i];
+    Node nd;
+    nd.lo = make_float4(s.bmin[0], s.bmin[1], s.bmin[2], s.bmax[0]);
+    nd.hi = make_float4(s.bmax[1], s.bmax[2], 0.f, 0.f);
+    for (int k = 0; k < 3; k++)
+      if (!(std::fabs(s.bmin[k]) <= 1.0995116e12f) || !(std::fabs(s.bmax[k]) <= 1.0995116e12f)) filter_ok = false;
+    st.push_back({i, 0, (int32_t)out.size()});
+    out.push_back(nd);
+    return SRT_OK;
+  };
+  srt_status rc = push_node(0);
+  if (rc) return rc;
+  while (!st.empty()) {
+    Frame f = st.back();
+    const srt_bvh_node& s = d->nodes[f.node];
+    const bool none = s.right == SRT_BVH_NONE;
+    if (f.stage == 0) {
+      int32_t pa, pb;
+      if (s.left < 0 && (none || s.right < 0)) {            // leaf node: one or two primitives
+        if (!leaf_prim(s.left, pa) || (!none && !leaf_prim(s.right, pb))) return fail(SRT_ERR_INVALID, "BVH primitive id out of range");
+        out[f.out_idx].hi.z = i2f(pa);
+        out[f.out_idx].hi.w = i2f(none ? NODE_NO_B : pb);
+        st.pop_back();
+        continue;
+      }
+      if (none) return fail(SRT_ERR_UNSUPPORTED, "SRT_BVH_NONE needs a primitive as the left child");
+      st.back().stage = 1;
+      if (s.left >= 0) { rc = push_node(s.left); if (rc) return rc; }
+      else {                                                 // primitive hanging under an inner node
+        if (!leaf_prim(s.left, pa)) return fail(SRT_ERR_INVALID, "BVH primitive id out of range");
+        Node p; p.lo = make_float4(0, 0, 0, 0); p.hi = make_float4(0, 0, i2f(pa), i2f(NODE_NO_BOX)); out.push_back(p);
+      }
+    } else if (f.stage == 1) {
+      st.back().stage = 2;
+      int32_t pb;
+      if (s.right >= 0) { rc = push_node(s.right); if (rc) return rc; }
+      else {
+        if (!leaf_prim(s.right, pb)) return fail(SRT_ERR_INVALID, "BVH primitive id out of range");
+        Node p; p.lo = make_float4(0, 0, 0, 0); p.hi = make_float4(0, 0, i2f(pb), i2f(NODE_NO_BOX)); out.push_back(p);
+      }
+    } else {
+      out[f.out_idx].hi.z = i2f((int32_t)out.size());        // skip link: first node after this subtree
+      out[f.out_idx].hi.w = i2f(NODE_INNER);
+      st.pop_back();
+    }
+  }
+  if (out.size() > (size_t)INT32_MAX) return fail(SRT_ERR_UNSUPPORTED, "BVH too large");
+  return SRT_OK;
+}
+
+template <typename T>
+static srt_status upload(srt_scene* s, const std::vector<T>& v, const T** dptr) {
+  void* p = nullptr;
+  size_t nb = v.size() * sizeof(T);
+  cudaError_t e = cudaMalloc(&p, nb ? nb : 16);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
+  s->buffers.push_back(p);
+  if (nb) CK(cudaMemcpyAsync(p, v.data(), nb, cudaMemcpyHostToDevice, s->dev->stream));
+  CK(cudaStreamSynchronize(s->dev->stream));   // v is a temporary of the caller
+  s->bytes += (int64_t)nb;
+  *dptr = static_cast<const T*>(p);
+  return SRT_OK;
+}
+
+static bool tex_is_image(const srt_scene_desc* d, int id) {
+  if (id < 0) return false;
+  const srt_texture& t = d->textures[id];
+  if (t.kind == SRT_TEX_IMAGE) return t.data != nullptr;
+  if (t.kind == SRT_TEX_CHECKER) return tex_is_image(d, t.even) || tex_is_image(d, t.odd);
+  return false;
+}
+
+extern "C" {
+
+void srt_scene_destroy(srt_scene* s) {
+  if (!s) return;
+  cudaSetDevice(s->dev->gpu);
+  for (auto t : s->texobjs) cudaDestroyTextureObject(t);
+  for (auto a : s->arrays) cudaFreeArray(a);
+  for (auto p : s->buffers) cudaFree(p);
+  delete s;
+}
+
+int64_t srt_scene_device_bytes(const srt_scene* s) { return s ? s->bytes : 0; }
+
+srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene** out) {
+  if (!dev || !d || !out) return fail(SRT_ERR_INVALID, "NULL argument");
+  *out = nullptr;
+  if (d->n_tri < 0 || d->n_sph < 0 || d->n_nodes < 0 || d->n_mat < 0 || d->n_tex < 0) return fail(SRT_ERR_INVALID, "negative count");
+  if (d->n_tri + d->n_sph > (int64_t)INT32_MAX || d->n_nodes > (int64_t)INT32_MAX) return fail(SRT_ERR_UNSUPPORTED, "scene too large");
+  CK(cudaSetDevice(dev->gpu));
+
+  // tables first: primitives are validated against them
+  for (int i = 0; i < d->n_tex; i++) {
+    const srt_texture& t = d->textures[i];
+    if (t.kind == SRT_TEX_CHECKER) {
+      for (int c : {t.even, t.odd})
+        if (c < 0 || c >= d->n_tex || d->textures[c].kind == SRT_TEX_CHECKER) return fail(SRT_ERR_UNSUPPORTED, "checker children must be solid or image textures");
+    } else if (t.kind == SRT_TEX_IMAGE) {
+      if (t.data && (t.width <= 0 || t.height <= 0 || t.bpp <= 0)) return fail(SRT_ERR_INVALID, "image texture with non-positive size");
+    } else if (t.kind != SRT_TEX_SOLID) return fail(SRT_ERR_INVALID, "unknown texture kind");
+  }
+  for (int i = 0; i < d->n_mat; i++) {
+    const srt_material& m = d->materials[i];
+    if (m.kind < SRT_MAT_PBR || m.kind > SRT_MAT_LIGHT) return fail(SRT_ERR_INVALID, "unknown material kind");
+    for (int t : {m.albedo_tex, m.normal_tex, m.metallic_tex, m.roughness_tex})
+      if (t >= d->n_tex) return fail(SRT_ERR_INVALID, "material texture id out of range");
+    if (m.kind == SRT_MAT_LIGHT && m.albedo_tex < 0) return fail(SRT_ERR_INVALID, "light without an emit texture");
+  }
+  for (int64_t i = 0; i < d->n_tri; i++) if (d->tri_mat[i] < 0 || d->tri_mat[i] >= d->n_mat) return fail(SRT_ERR_INVALID, "triangle material id out of range");
+  for (int64_t i = 0; i < d->n_sph; i++) if (d->sph_mat[i] < 0 || d->sph_mat[i] >= d->n_mat) return fail(SRT_ERR_INVALID, "sphere material id out of range");
+
+  std::vector<Node> nodes;
+  bool filter_ok = true;
+  srt_status rc = thread_bvh(d, nodes, filter_ok);
+  if (rc) return rc;
+
+  srt_scene* s = new srt_scene;
+  s->dev = dev;
+#define SCK(expr) do { srt_status rc_ = (expr); if (rc_) { srt_scene_destroy(s); return rc_; } } while (0)
+  SCK(upload(s, nodes, &s->sc.nodes));
+  s->sc.n_nodes = (int)nodes.size();
+  s->sc.filter_ok = filter_ok ? 1 : 0;
+  s->node_bytes = nodes.size() * sizeof(Node);
+  s->nodes_in_smem = s->node_bytes > 0 && s->node_bytes <= dev->smem_optin;
+
+  std::vector<Tri> tris((size_t)d->n_tri);
+  std::vector<TriUV> uvs((size_t)d->n_tri);
+  for (int64_t i = 0; i < d->n_tri; i++) {
+    const float *a = d->tri_v0 + 3 * i, *b = d->tri_v1 + 3 * i, *c = d->tri_v2 + 3 * i;
+    tris[i].a = make_float4(a[0], a[1], a[2], 0); tris[i].b = make_float4(b[0], b[1], b[2], 0);
+    tris[i].c = make_float4(c[0], c[1], c[2], 0); tris[i].d = make_float4(0, i2f(d->tri_mat[i]), 0, 0);
+    uvs[i].a = make_float4(d->tri_uv0[2 * i], d->tri_uv0[2 * i + 1], d->tri_uv1[2 * i], d->tri_uv1[2 * i + 1]);
+    uvs[i].b = make_float4(d->tri_uv2[2 * i], d->tri_uv2[2 * i + 1], 0, 0);
+  }
+  SCK(upload(s, tris, &s->sc.tris));
+  SCK(upload(s, uvs, &s->sc.tri_uv));
+  s->sc.n_tri = (int)d->n_tri;
+  std::vector<Sph> sphs((size_t)d->n_sph);
+  for (int64_t j = 0; j < d->n_sph; j++) {
+    const float *a = d->sph_c0 + 3 * j, *b = d->sph_c1 + 3 * j;
+    bool moving = a[0] != b[0] || a[1] != b[1] || a[2] != b[2];      // center0 != center1, sphere.h:48
+    sphs[j].a = make_float4(a[0], a[1], a[2], d->sph_r[j]);
+    sphs[j].b = make_float4(b[0], b[1], b[2], d->sph_t0[j]);
+    sphs[j].c = make_float4(d->sph_t1[j], i2f(d->sph_mat[j]), moving ? 1.0f : 0.0f, 0);
+  }
+  SCK(upload(s, sphs, &s->sc.sphs));
+  s->sc.n_sph = (int)d->n_sph;
+
+  // textures: texel (i,j) = (px[0],px[1],px[2],255), px = data + j*bpp*w + i*bpp; bytes past the end read 0
+  std::vector<Tex> texs((size_t)d->n_tex);
+  for (int i = 0; i < d->n_tex; i++) {
+    const srt_texture& t = d->textures[i];
+    Tex x; memset(&x, 0, sizeof x);
+    x.kind = t.kind; x.r = t.color[0]; x.g = t.color[1]; x.b = t.color[2]; x.even = t.even; x.odd = t.odd;
+    x.w = t.width; x.h = t.height; x.missing = (t.kind == SRT_TEX_IMAGE && !t.data) ? 1 : 0;
+    if (t.kind == SRT_TEX_IMAGE && t.data) {
+      const size_t n = (size_t)t.width * t.height * t.bpp;
+      std::vector<uchar4> rgba((size_t)t.width * t.height);
+      for (int j = 0; j < t.height; j++)
+        for (int k = 0; k < t.width; k++) {
+          size_t off = (size_t)j * ((size_t)t.bpp * t.width) + (size_t)k * t.bpp;
+          uchar4 p;
+          p.x = off < n ? t.data[off] : 0; p.y = off + 1 < n ? t.data[off + 1] : 0; p.z = off + 2 < n ? t.data[off + 2] : 0; p.w = 255;
+          rgba[(size_t)j * t.width + k] = p;
+        }
+      cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+      cudaArray_t arr = nullptr;
+      cudaError_t e = cudaMallocArray(&arr, &fmt, t.width, t.height);
+      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaMallocArray: ") + cudaGetErrorString(e)); }
+      s->arrays.push_back(arr);
+      e = cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)t.width * 4, (size_t)t.width * 4, t.height, cudaMemcpyHostToDevice);
+      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaMemcpy2DToArray: ") + cudaGetErrorString(e)); }
+      cudaResourceDesc rd; memset(&rd, 0, sizeof rd); rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+      cudaTextureDesc td; memset(&td, 0, sizeof td);
+      td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp; td.filterMode = cudaFilterModePoint;
+      td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+      e = cudaCreateTextureObject(&x.obj, &rd, &td, nullptr);
+      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaCreateTextureObject: ") + cudaGetErrorString(e)); }
+      s->texobjs.push_back(x.obj);
+      s->bytes += (int64_t)rgba.size() * 4;
+    }
+    texs[i] = x;
+  }
+  SCK(upload(s, texs, &s->sc.texs));
+  s->sc.n_tex = d->n_tex;
+
+  std::vector<Mat> mats((size_t)d->n_mat);
+  for (int i = 0; i < d->n_mat; i++) {
+    const srt_material& m = d->materials[i];
+    Mat x; memset(&x, 0, sizeof x);
+    x.kind = m.kind; x.albedo_tex = m.albedo_tex; x.normal_tex = m.normal_tex; x.metallic_tex = m.metallic_tex;
+    x.roughness_tex = m.roughness_tex; x.metalness = m.metalness; x.roughness = m.roughness;
+    for (int k = 0; k < 4; k++) x.albedo[k] = m.albedo[k];
+    x.fuzz = m.fuzz; x.ir = m.ir;
+    if (m.kind != SRT_MAT_PBR) { x.normal_tex = x.metallic_tex = x.roughness_tex = -1; if (m.kind != SRT_MAT_LIGHT) x.albedo_tex = -1; }
+    if (tex_is_image(d, x.albedo_tex) || tex_is_image(d, x.normal_tex) || tex_is_image(d, x.metallic_tex) || tex_is_image(d, x.roughness_tex))
+      x.flags |= MAT_NEEDS_UV;
+    if (x.normal_tex >= 0) x.flags |= MAT_NEEDS_TBN;
+    mats[i] = x;
+  }
+  SCK(upload(s, mats, &s->sc.mats));
+  s->sc.n_mat = d->n_mat;
+#undef SCK
+
+  if (d->n_tri > 0) {
+    k_setup_tris<<<(unsigned)((d->n_tri + 255) / 256), 256, 0, dev->stream>>>(const_cast<Tri*>(s->sc.tris), (int)d->n_tri);
+    cudaError_t e = cudaStreamSynchronize(dev->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("k_setup_tris: ") + cudaGetErrorString(e)); }
+  }
+  *out = s;
+  return SRT_OK;
+}
+
+}  // extern "C"
+
+#include "srt_launch.cuh"

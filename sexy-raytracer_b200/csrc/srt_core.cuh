@@ -1,0 +1,237 @@
+// srt_core.cuh — device-side scene layout, exact fp32 helpers and the ordered BVH traversal.
+//
+// Arithmetic contract: every comparison that decides hit/miss, and the
+// values t / p / normal / uv of an accepted hit, are evaluated as the reference evaluates them —
+// same operation order, no FMA contraction (this translation unit is compiled with -fmad=false;
+// -prec-div / -prec-sqrt stay at their IEEE defaults, denormals stay on).  FMAs appear only where
+// written explicitly (fmaf) in the *filtered* box predicate, whose result is proven equal to the
+// exact one or else recomputed exactly.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <float.h>
+
+namespace srt {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+// Eigen's 3-vector dot (Redux.h:101-115): a0*b0 + (a1*b1 + a2*b2)
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + (a.y * b.y + a.z * b.z); }
+// Eigen's cross (OrthoMethods.h:47-49)
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+// vec3.h:29-31
+__device__ __forceinline__ float length_squared(V3 v) { return v.x * v.x + v.y * v.y + v.z * v.z; }
+// vec3.h:33-35
+__device__ __forceinline__ float length(V3 v) { return sqrtf(length_squared(v)); }
+// vec3.h:54-60
+__device__ __forceinline__ V3 unit_vector(V3 v) {
+  float len = length(v);
+  if (len != 0) return mk(v.x / len, v.y / len, v.z / len);
+  return v;
+}
+// globals.h:17-24
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
+#define SRT_PI 3.1415926535897932385f  /* globals.h:15 */
+
+struct Ray { V3 o, d; float time; };
+
+// ---- device scene -----------------------------------------------------------------------------
+// BVH node, 32 bytes, "threaded" form of the caller's pre-order tree (include/srt.h: srt_bvh_node).
+// The reference's traversal order is fixed (bvh.h:97-105: left subtree, then right subtree), so the
+// recursion is equivalent to walking the pre-order array with a skip link — no stack:
+//   inner node : box hit -> i+1 (its left child is next in pre-order);  box miss -> skip
+//   leaf node  : box hit -> test prim a, then prim b;                   then i+1 either way
+// lo = (min.x, min.y, min.z, max.x)   hi = (max.y, max.z, w6, w7)
+//   inner: w6 = skip index, w7 = NODE_INNER;  leaf: w6 = prim a, w7 = prim b | NODE_NO_B | NODE_NO_BOX
+struct Node { float4 lo, hi; };
+#define NODE_INNER  ((int)0x80000000)
+#define NODE_NO_B   (-1)     /* span-1 node of the reference (bvh.h:67-69): one primitive */
+#define NODE_NO_BOX (-2)     /* a primitive hanging directly under an inner node: no box of its own */
+
+// triangle, 64 bytes: positions + the reference's un-normalised normal N = (v1-v0)x(v2-v0)
+// (model.h:276-283) and plane term dd = -(N.v0) (model.h:125), precomputed with the same arithmetic
+struct Tri { float4 a, b, c, d; };   // a=(v0,N.x) b=(v1,N.y) c=(v2,N.z) d=(dd, mat, -, -)
+struct TriUV { float4 a, b; };       // a=(uv0, uv1) b=(uv2, -, -)
+struct Sph { float4 a, b, c; };      // a=(c0, r) b=(c1, t0) c=(t1, mat, moving, -)
+
+struct Tex {
+  int kind;                 // SRT_TEX_*
+  float r, g, b;            // SOLID
+  int even, odd;            // CHECKER
+  int w, h;                 // IMAGE
+  int missing;              // IMAGE: file was missing -> (1,0,1)
+  int pad;
+  cudaTextureObject_t obj;  // IMAGE: uchar4 array, point sampled, unnormalised coordinates
+};
+
+#define MAT_NEEDS_UV  1
+#define MAT_NEEDS_TBN 2
+struct Mat {
+  int kind, albedo_tex, normal_tex, metallic_tex;
+  int roughness_tex, flags; float metalness, roughness;
+  float albedo[4];
+  float fuzz, ir, pad0, pad1;
+};
+
+struct Scene {
+  const Node*  nodes;  int n_nodes;
+  const Tri*   tris;   int n_tri;
+  const TriUV* tri_uv;
+  const Sph*   sphs;   int n_sph;
+  const Mat*   mats;   int n_mat;
+  const Tex*   texs;   int n_tex;
+  int filter_ok;       // every box coordinate is finite and small enough for the filtered predicate
+};
+
+// ---- aabb::hit, aabb.h:11-27 --------------------------------------------------------------------
+// exact form: six true divisions, fminf/fmaxf (NaN -> the other operand, as in C), tMax <= tMin misses
+__device__ __forceinline__ bool box_hit_exact(const float4& lo, const float4& hi, const Ray& r, float tMin, float tMax) {
+  float a, b, t0, t1;
+  a = (lo.x - r.o.x) / r.d.x; b = (lo.w - r.o.x) / r.d.x;
+  t0 = fminf(a, b); t1 = fmaxf(a, b); tMin = fmaxf(t0, tMin); tMax = fminf(t1, tMax);
+  if (tMax <= tMin) return false;
+  a = (lo.y - r.o.y) / r.d.y; b = (hi.x - r.o.y) / r.d.y;
+  t0 = fminf(a, b); t1 = fmaxf(a, b); tMin = fmaxf(t0, tMin); tMax = fminf(t1, tMax);
+  if (tMax <= tMin) return false;
+  a = (lo.z - r.o.z) / r.d.z; b = (hi.y - r.o.z) / r.d.z;
+  t0 = fminf(a, b); t1 = fmaxf(a, b); tMin = fmaxf(t0, tMin); tMax = fminf(t1, tMax);
+  if (tMax <= tMin) return false;
+  return true;
+}
+
+// Filtered predicate.  aabb::hit only returns a bool, so a cheaper evaluation may stand in for it
+// wherever it provably gives the same answer.  With id = fl(1/d), oid = fl(o*id) the slab bound
+// a' = fma(c, id, -oid) differs from the reference's fl(fl(c-o)/d) by at most
+// 4.02u|q| + 1.01u|o/d| (u = 2^-24, q the true quotient); max/min over the axes keep that bound.
+// The interval test is decided by the filter when |hi - lo| exceeds 2^-20 (M + |lo| + |hi|) + 1e-30,
+// M = max|oid| — a 4x margin over the bound — and by box_hit_exact otherwise.  Rays with a zero,
+// non-finite or extreme direction component never use the filter (ok == 0).
+struct RayAux { float idx, idy, idz, oidx, oidy, oidz, M; int ok; };
+
+__device__ __forceinline__ RayAux make_aux(const Ray& r, int scene_filter_ok) {
+  RayAux a;
+  a.idx = 1.0f / r.d.x; a.idy = 1.0f / r.d.y; a.idz = 1.0f / r.d.z;
+  a.oidx = r.o.x * a.idx; a.oidy = r.o.y * a.idy; a.oidz = r.o.z * a.idz;
+  float mi = fmaxf(fabsf(a.idx), fmaxf(fabsf(a.idy), fabsf(a.idz)));
+  a.M = fmaxf(fabsf(a.oidx), fmaxf(fabsf(a.oidy), fabsf(a.oidz)));
+  // mi <= 2^40 and M <= 2^60 fail for NaN/inf as well; box coordinates are <= 2^40 when scene_filter_ok
+  a.ok = scene_filter_ok && (mi <= 1.0995116e12f) && (a.M <= 1.1529215e18f) && (r.time == r.time);
+  return a;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ bool box_hit(const float4& lo, const float4& hi, const Ray& r, const RayAux& x, float tMin,
+                                        float tMax, unsigned long long* exact_count) {
+  if (x.ok) {
+    float ax = fmaf(lo.x, x.idx, -x.oidx), bx = fmaf(lo.w, x.idx, -x.oidx);
+    float ay = fmaf(lo.y, x.idy, -x.oidy), by = fmaf(hi.x, x.idy, -x.oidy);
+    float az = fmaf(lo.z, x.idz, -x.oidz), bz = fmaf(hi.y, x.idz, -x.oidz);
+    float l = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tMin));
+    float h = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tMax));
+    float slack = fmaf(9.5367432e-7f, x.M + fabsf(l) + fabsf(h), 1e-30f);
+    float diff = h - l;
+    if (diff > slack) return true;
+    if (diff < -slack) return false;
+    // tMax = +inf and an unbounded slab give h = inf: diff = inf > slack handled above; NaN falls through
+  }
+  if (COUNT) ++*exact_count;
+  return box_hit_exact(lo, hi, r, tMin, tMax);
+}
+
+// ---- triangle::hit decision, model.h:104-154 ---------------------------------------------------------
+// plane intersection + three inside-edge tests, back-face culled, NO tMax test.  Returns t on accept.
+__device__ __forceinline__ bool tri_hit(const Tri* __restrict__ tris, int i, const Ray& r, float tMin, float& tOut) {
+  const float4 A = __ldg(&tris[i].a), B = __ldg(&tris[i].b), C = __ldg(&tris[i].c);
+  const float dd = __ldg(&tris[i].d.x);
+  V3 N = mk(A.w, B.w, C.w);
+  float NdotDir = dot(N, r.d);
+  if (fabsf(NdotDir) < FLT_EPSILON) return false;       // model.h:119
+  if (NdotDir > 0) return false;                        // model.h:122 (dir.dot(normal): same products, same sum)
+  float t = -(dot(N, r.o) + dd) / NdotDir;              // model.h:125-126
+  if (t < tMin) return false;                           // model.h:128; NaN t passes, as in the reference
+  V3 v0 = mk(A.x, A.y, A.z), v1 = mk(B.x, B.y, B.z), v2 = mk(C.x, C.y, C.z);
+  V3 p = mk(r.o.x + t * r.d.x, r.o.y + t * r.d.y, r.o.z + t * r.d.z);
+  if (dot(N, cross(v1 - v0, p - v0)) < 0) return false;  // model.h:136-140
+  if (dot(N, cross(v2 - v1, p - v1)) < 0) return false;  // model.h:143-147
+  if (dot(N, cross(v0 - v2, p - v2)) < 0) return false;  // model.h:150-154
+  tOut = t;
+  return true;
+}
+
+// sphere.h:47-52
+__device__ __forceinline__ V3 sph_center(const float4& a, const float4& b, const float4& c, float time) {
+  V3 c0 = mk(a.x, a.y, a.z);
+  if (c.z != 0.0f) {    // center0 != center1
+    V3 c1 = mk(b.x, b.y, b.z);
+    float f = (time - b.w) / (c.x - b.w);
+    return c0 + f * (c1 - c0);
+  }
+  return c0;
+}
+
+// sphere::hit decision, sphere.h:54-72: nearest root in the INCLUSIVE range [tMin, tMax]
+__device__ __forceinline__ bool sph_hit(const Sph* __restrict__ sphs, int j, const Ray& r, float tMin, float tMax, float& tOut) {
+  const float4 a = __ldg(&sphs[j].a), b = __ldg(&sphs[j].b), c = __ldg(&sphs[j].c);
+  V3 oc = r.o - sph_center(a, b, c, r.time);
+  float aa = length_squared(r.d);
+  float halfB = dot(oc, r.d);
+  float cc = length_squared(oc) - a.w * a.w;
+  float disc = halfB * halfB - aa * cc;
+  if (disc < 0.0f) return false;
+  float sqrtd = sqrtf(disc);
+  float root = (-halfB - sqrtd) / aa;
+  if (root < tMin || root > tMax) {
+    root = (-halfB + sqrtd) / aa;
+    if (root < tMin || root > tMax) return false;
+  }
+  tOut = root;
+  return true;
+}
+
+struct Counters { unsigned long long nodes, leaves, exact; };
+
+// hittableList::hit -> bvhNode::hit (hittablelist.h:33-47, bvh.h:97-105) in the threaded form.
+// Rule: walk in pre-order; one running tCur = t of the most recently ACCEPTED leaf
+// (initially tMax); boxes and spheres are tested against [tMin, tCur]; triangles ignore tCur; every
+// accept overwrites the record.  `nodes` may point to shared memory.
+template <bool COUNT>
+__device__ __forceinline__ void traverse(const Scene& sc, const Node* nodes, const Ray& r, float tMin, float tMax,
+                                         int& prim, float& tHit, Counters* cnt) {
+  const RayAux aux = make_aux(r, sc.filter_ok);
+  float tCur = tMax;
+  prim = -1;
+  int i = 0;
+  const int n = sc.n_nodes;
+  while (i < n) {
+    const float4 lo = nodes[i].lo, hi = nodes[i].hi;
+    const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
+    if (COUNT) ++cnt->nodes;
+    bool hit = (w7 == NODE_NO_BOX) ? true : box_hit<COUNT>(lo, hi, r, aux, tMin, tCur, COUNT ? &cnt->exact : nullptr);
+    if (w7 == NODE_INNER) {
+      i = hit ? i + 1 : w6;
+    } else {
+      if (hit) {
+#pragma unroll 1
+        for (int k = 0; k < 2; k++) {
+          int p = k == 0 ? w6 : w7;
+          if (p < 0) break;
+          if (COUNT) ++cnt->leaves;
+          float t;
+          bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, tMin, t) : sph_hit(sc.sphs, p - sc.n_tri, r, tMin, tCur, t);
+          if (acc) { tCur = t; prim = p; }
+        }
+      }
+      i = i + 1;
+    }
+  }
+  tHit = tCur;
+}
+
+}  // namespace srt

@@ -1,0 +1,239 @@
+// srt_launch.cuh — compute entry points of the C ABI (included at the end of srt_b200.cu).
+#pragma once
+
+namespace {
+
+struct DevBuf {   // scoped device allocation
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
+  template <typename T> T* as() { return static_cast<T*>(p); }
+};
+
+struct RenderPlan { RenderArgs A; int blocks, threads; size_t smem; };
+
+srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_params* P, RenderPlan& plan) {
+  if (!s || !cam || !P) return fail(SRT_ERR_INVALID, "NULL argument");
+  if (P->width < 2 || P->height < 2) return fail(SRT_ERR_INVALID, "width and height must be >= 2 (main.cpp:210-211 divide by W-1, H-1)");
+  if ((int64_t)P->width * P->height > (int64_t)INT32_MAX / 4) return fail(SRT_ERR_UNSUPPORTED, "frame too large");
+  if (P->spp <= 0 || P->max_bounce < 0 || P->sample_begin < 0 || P->sample_count < 0) return fail(SRT_ERR_INVALID, "bad sample/bounce counts");
+  if (P->variant != 0 && P->variant != 1) return fail(SRT_ERR_UNSUPPORTED, "render variant not built (1 = megakernel)");
+  RenderArgs& A = plan.A;
+  A.cam = *cam; A.W = P->width; A.H = P->height;
+  A.sample_begin = P->sample_begin; A.sample_count = P->sample_count > 0 ? P->sample_count : P->spp;
+  A.max_bounce = P->max_bounce; A.rr_begin = P->rr_begin;
+  A.bg[0] = P->background[0]; A.bg[1] = P->background[1]; A.bg[2] = P->background[2];
+  A.seed = P->seed;
+  A.tiles_x = (A.W + 7) / 8;
+  A.n_tiles = A.tiles_x * ((A.H + 3) / 4);
+
+  srt_device* dev = s->dev;
+  plan.threads = 512;
+  plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
+  int per_sm = 0;
+  cudaError_t e;
+  if (dev->counters) {
+    e = cudaFuncSetAttribute(k_render_mega<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_mega<true>, plan.threads, plan.smem);
+  } else {
+    e = cudaFuncSetAttribute(k_render_mega<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_mega<false>, plan.threads, plan.smem);
+  }
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(e)); }
+  if (per_sm < 1) return fail(SRT_ERR_CUDA, "render kernel does not fit on an SM");
+  plan.blocks = dev->sm_count * per_sm;           // persistent grid: every CTA resident, a multiple of the SM count
+
+  // work units: enough (tile, chunk) pairs per resident warp that the tail is ~1 %, chunks of >= 8 samples
+  const long long warps = (long long)plan.blocks * (plan.threads / 32);
+  const long long want_units = warps * 64;
+  long long n_chunks = (want_units + A.n_tiles - 1) / A.n_tiles;
+  if (n_chunks < 1) n_chunks = 1;
+  int chunk = (int)((A.sample_count + n_chunks - 1) / n_chunks);
+  if (chunk < 8) chunk = 8;
+  if (chunk > A.sample_count) chunk = A.sample_count;
+  A.chunk = chunk;
+  A.n_chunks = (A.sample_count + chunk - 1) / chunk;
+  A.n_units = (long long)A.n_tiles * A.n_chunks;
+  return SRT_OK;
+}
+
+srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
+  srt_device* dev = s->dev;
+  CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
+  CK(cudaEventRecord(dev->ev0, dev->stream));
+  if (dev->counters)
+    k_render_mega<true><<<plan.blocks, plan.threads, plan.smem, dev->stream>>>(s->sc, s->nodes_in_smem, plan.A, accum_dev, dev->d_counters);
+  else
+    k_render_mega<false><<<plan.blocks, plan.threads, plan.smem, dev->stream>>>(s->sc, s->nodes_in_smem, plan.A, accum_dev, dev->d_counters);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(dev->ev1, dev->stream));
+  unsigned long long h[8];
+  CK(cudaMemcpyAsync(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->paths = h[0]; stats->segments = h[1]; stats->node_visits = h[2]; stats->leaf_tests = h[3];
+    float ms = 0; CK(cudaEventElapsedTime(&ms, dev->ev0, dev->ev1));
+    stats->kernel_ms = ms; stats->launches = 1;
+  }
+  return SRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+srt_status srt_render_accumulate(srt_scene* s, const srt_camera* cam, const srt_render_params* P, float* accum_dev,
+                                 srt_stats* stats) {
+  if (!accum_dev) return fail(SRT_ERR_INVALID, "accum_dev is NULL");
+  RenderPlan plan;
+  srt_status rc = plan_render(s, cam, P, plan);
+  if (rc) return rc;
+  CK(cudaSetDevice(s->dev->gpu));
+  return run_render(s, plan, accum_dev, stats);
+}
+
+srt_status srt_resolve(srt_device* dev, const float* sum_dev, int32_t W, int32_t H, int32_t spp, uint8_t* rgba8_dev) {
+  if (!dev || !sum_dev || !rgba8_dev || W <= 0 || H <= 0 || spp <= 0) return fail(SRT_ERR_INVALID, "bad argument");
+  CK(cudaSetDevice(dev->gpu));
+  int n = W * H;
+  k_resolve<<<(n + 255) / 256, 256, 0, dev->stream>>>(sum_dev, n, spp, reinterpret_cast<uchar4*>(rgba8_dev));
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+srt_status srt_render(srt_scene* s, const srt_camera* cam, const srt_render_params* P, float* out_sum_rgb,
+                      uint8_t* out_rgba8, srt_stats* stats) {
+  RenderPlan plan;
+  srt_status rc = plan_render(s, cam, P, plan);
+  if (rc) return rc;
+  srt_device* dev = s->dev;
+  CK(cudaSetDevice(dev->gpu));
+  const size_t n = (size_t)P->width * P->height;
+  DevBuf acc, rgba;
+  CK(acc.alloc(n * 3 * sizeof(float)));
+  CK(cudaMemsetAsync(acc.p, 0, n * 3 * sizeof(float), dev->stream));
+  rc = run_render(s, plan, acc.as<float>(), stats);
+  if (rc) return rc;
+  if (out_rgba8) {
+    CK(rgba.alloc(n * 4));
+    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, dev->stream>>>(acc.as<float>(), (int)n, P->spp, rgba.as<uchar4>());
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_rgba8, rgba.p, n * 4, cudaMemcpyDeviceToHost, dev->stream));
+    if (stats) stats->launches += 1;
+  }
+  if (out_sum_rgb) CK(cudaMemcpyAsync(out_sum_rgb, acc.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_min, float t_max, srt_hit* out_hits) {
+  if (!s || n < 0 || (n > 0 && (!rays || !out_hits))) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  srt_device* dev = s->dev;
+  CK(cudaSetDevice(dev->gpu));
+  DevBuf dr, dh;
+  CK(dr.alloc((size_t)n * sizeof(srt_ray)));
+  CK(dh.alloc((size_t)n * sizeof(srt_hit)));
+  CK(cudaMemcpyAsync(dr.p, rays, (size_t)n * sizeof(srt_ray), cudaMemcpyHostToDevice, dev->stream));
+  const int threads = 256;
+  size_t smem = s->nodes_in_smem ? s->node_bytes : 0;
+  long long want = (n + threads - 1) / threads;
+  int blocks = (int)(want < (long long)dev->sm_count * 8 ? want : (long long)dev->sm_count * 8);
+  CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
+  if (dev->counters) {
+    CK(cudaFuncSetAttribute(k_trace_rays<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin));
+    k_trace_rays<true><<<blocks, threads, smem, dev->stream>>>(s->sc, s->nodes_in_smem, dr.as<srt_ray>(), n, t_min, t_max, dh.as<srt_hit>(), dev->d_counters);
+  } else {
+    CK(cudaFuncSetAttribute(k_trace_rays<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin));
+    k_trace_rays<false><<<blocks, threads, smem, dev->stream>>>(s->sc, s->nodes_in_smem, dr.as<srt_ray>(), n, t_min, t_max, dh.as<srt_hit>(), dev->d_counters);
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_hits, dh.p, (size_t)n * sizeof(srt_hit), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+// node visits / leaf tests / exact (unfiltered) box tests of the last srt_trace_rays or render call
+srt_status srt_last_counters(srt_device* dev, uint64_t* out3) {
+  if (!dev || !out3) return fail(SRT_ERR_INVALID, "NULL argument");
+  unsigned long long h[8];
+  CK(cudaSetDevice(dev->gpu));
+  CK(cudaMemcpy(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost));
+  out3[0] = h[2]; out3[1] = h[3]; out3[2] = h[4];
+  return SRT_OK;
+}
+
+srt_status srt_shade_kat(srt_scene* s, const srt_ray* rays_in, const srt_hit* hits, const float* xi, int64_t n,
+                         float* out_att, float* out_emit, srt_ray* out_rays, int32_t* out_scattered) {
+  if (!s || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  for (int64_t i = 0; i < n; i++) if (hits[i].mat < 0 || hits[i].mat >= s->sc.n_mat) return fail(SRT_ERR_INVALID, "hit material id out of range");
+  srt_device* dev = s->dev;
+  CK(cudaSetDevice(dev->gpu));
+  DevBuf dr, dh, dx, da, de, dout, ds;
+  CK(dr.alloc(n * sizeof(srt_ray))); CK(dh.alloc(n * sizeof(srt_hit))); CK(dx.alloc(n * 16)); CK(da.alloc(n * 12));
+  CK(de.alloc(n * 12)); CK(dout.alloc(n * sizeof(srt_ray))); CK(ds.alloc(n * 4));
+  CK(cudaMemcpyAsync(dr.p, rays_in, n * sizeof(srt_ray), cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemcpyAsync(dh.p, hits, n * sizeof(srt_hit), cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemcpyAsync(dx.p, xi, n * 16, cudaMemcpyHostToDevice, dev->stream));
+  k_shade_kat<<<(unsigned)((n + 127) / 128), 128, 0, dev->stream>>>(s->sc, dr.as<srt_ray>(), dh.as<srt_hit>(), dx.as<float>(), n,
+                                                                   da.as<float>(), de.as<float>(), dout.as<srt_ray>(), ds.as<int>());
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_att, da.p, n * 12, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaMemcpyAsync(out_emit, de.p, n * 12, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaMemcpyAsync(out_rays, dout.p, n * sizeof(srt_ray), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaMemcpyAsync(out_scattered, ds.p, n * 4, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+srt_status srt_texture_kat(srt_scene* s, int32_t tex, const float* uvp, int64_t n, float* out_rgb) {
+  if (!s || n < 0 || tex < 0 || tex >= s->sc.n_tex) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  srt_device* dev = s->dev;
+  CK(cudaSetDevice(dev->gpu));
+  DevBuf di, dout;
+  CK(di.alloc(n * 20)); CK(dout.alloc(n * 12));
+  CK(cudaMemcpyAsync(di.p, uvp, n * 20, cudaMemcpyHostToDevice, dev->stream));
+  k_texture_kat<<<(unsigned)((n + 127) / 128), 128, 0, dev->stream>>>(s->sc, tex, di.as<float>(), n, dout.as<float>());
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_rgb, dout.p, n * 12, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+srt_status srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* in, int64_t n, srt_ray* out_rays) {
+  if (!dev || !cam || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  CK(cudaSetDevice(dev->gpu));
+  DevBuf di, dout;
+  CK(di.alloc(n * 20)); CK(dout.alloc(n * sizeof(srt_ray)));
+  CK(cudaMemcpyAsync(di.p, in, n * 20, cudaMemcpyHostToDevice, dev->stream));
+  k_getray_kat<<<(unsigned)((n + 127) / 128), 128, 0, dev->stream>>>(*cam, di.as<float>(), n, dout.as<srt_ray>());
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_rays, dout.p, n * sizeof(srt_ray), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+srt_status srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_render_params* P, const int32_t* pixel_xy,
+                            const int32_t* sample, int64_t n, srt_ray* out_rays) {
+  if (!dev || !cam || !P || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  CK(cudaSetDevice(dev->gpu));
+  RenderArgs A; memset(&A, 0, sizeof A);
+  A.cam = *cam; A.W = P->width; A.H = P->height; A.seed = P->seed;
+  DevBuf dp, dsm, dout;
+  CK(dp.alloc(n * 8)); CK(dsm.alloc(n * 4)); CK(dout.alloc(n * sizeof(srt_ray)));
+  CK(cudaMemcpyAsync(dp.p, pixel_xy, n * 8, cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemcpyAsync(dsm.p, sample, n * 4, cudaMemcpyHostToDevice, dev->stream));
+  k_primary_rays<<<(unsigned)((n + 127) / 128), 128, 0, dev->stream>>>(A, dp.as<int>(), dsm.as<int>(), n, dout.as<srt_ray>());
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_rays, dout.p, n * sizeof(srt_ray), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+"""Thin ctypes binding of libsrt_b200.so (include/srt.h).  No arithmetic happens in Python and there
+is no fallback: if the CUDA library is missing or a call fails, an exception is raised.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsrt_b200.so")
+_lib = None
+
+
+class SrtError(RuntimeError):
+    pass
+
+
+def lib():
+    """The loaded C-ABI library (loaded once).  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SrtError("libsrt_b200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                           "there is no CPU fallback")
+        _lib = abi.bind(C.CDLL(LIB_PATH))
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        L = lib()
+        raise SrtError("%s: %s" % (L.srt_status_string(rc).decode(), L.srt_last_error().decode()))
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Device:
+    """srt_device: one GPU.  Replaces glDevice::init/terminate (gl.h:28,31)."""
+
+    def __init__(self, gpu_id=0):
+        self.h = C.c_void_p()
+        _check(lib().srt_device_create(gpu_id, C.byref(self.h)))
+        self.gpu_id = gpu_id
+
+    def close(self):
+        if self.h:
+            lib().srt_device_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def set_counters(self, on):
+        _check(lib().srt_set_counters(self.h, 1 if on else 0))
+
+    def last_counters(self):
+        out = np.zeros(3, np.uint64)
+        _check(lib().srt_last_counters(self.h, _ptr(out)))
+        return {"node_visits": int(out[0]), "leaf_tests": int(out[1]), "exact_box_tests": int(out[2])}
+
+    @property
+    def stream(self):
+        return lib().srt_device_stream(self.h)
+
+    def upload(self, scene):
+        return DeviceScene(self, scene)
+
+    def resolve_dev(self, sum_dev_ptr, W, H, spp, rgba_dev_ptr):
+        _check(lib().srt_resolve(self.h, sum_dev_ptr, W, H, spp, rgba_dev_ptr))
+
+    def getray_kat(self, camera, inp):
+        inp = np.ascontiguousarray(inp, np.float32).reshape(-1, 5)
+        out = np.zeros(len(inp), abi.RAY_DTYPE)
+        _check(lib().srt_getray_kat(self.h, C.byref(camera), _ptr(inp), len(inp), _ptr(out)))
+        return out
+
+    def primary_rays(self, camera, params, pixel_xy, sample):
+        pixel_xy = np.ascontiguousarray(pixel_xy, np.int32).reshape(-1, 2)
+        sample = np.ascontiguousarray(sample, np.int32)
+        out = np.zeros(len(sample), abi.RAY_DTYPE)
+        _check(lib().srt_primary_rays(self.h, C.byref(camera), C.byref(params), _ptr(pixel_xy), _ptr(sample), len(sample),
+                                      _ptr(out)))
+        return out
+
+
+class DeviceScene:
+    """srt_scene: a flattened scene resident on the GPU."""
+
+    def __init__(self, device, scene):
+        self.device, self.scene = device, scene
+        self.h = C.c_void_p()
+        d = scene.desc()
+        _check(lib().srt_scene_create(device.h, C.byref(d), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().srt_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    @property
+    def device_bytes(self):
+        return int(lib().srt_scene_device_bytes(self.h))
+
+    def trace(self, rays, t_min=0.001, t_max=float("inf")):
+        rays = np.ascontiguousarray(rays, abi.RAY_DTYPE)
+        hits = np.zeros(len(rays), abi.HIT_DTYPE)
+        _check(lib().srt_trace_rays(self.h, _ptr(rays), len(rays), t_min, t_max, _ptr(hits)))
+        return hits
+
+    def render(self, params=None, want_sum=True, want_rgba=True, camera=None):
+        """srt_render with host buffers -> (sum [H,W,3] f32 | None, rgba [H,W,4] u8 | None, Stats)"""
+        P = params if params is not None else self.scene.render_params()
+        cam = camera if camera is not None else self.scene.camera_struct()
+        acc = np.zeros((P.height, P.width, 3), np.float32) if want_sum else None
+        rgba = np.zeros((P.height, P.width, 4), np.uint8) if want_rgba else None
+        st = abi.Stats()
+        _check(lib().srt_render(self.h, C.byref(cam), C.byref(P), _ptr(acc) if want_sum else None,
+                                _ptr(rgba) if want_rgba else None, C.byref(st)))
+        return acc, rgba, st
+
+    def render_accumulate(self, accum_dev_ptr, params=None, camera=None):
+        """Adds this call's samples into a device buffer [H*W*3] f32 (e.g. a torch tensor's data_ptr())."""
+        P = params if params is not None else self.scene.render_params()
+        cam = camera if camera is not None else self.scene.camera_struct()
+        st = abi.Stats()
+        _check(lib().srt_render_accumulate(self.h, C.byref(cam), C.byref(P), accum_dev_ptr, C.byref(st)))
+        return st
+
+    def shade_kat(self, rays, hits, rvec_xi):
+        rays = np.ascontiguousarray(rays, abi.RAY_DTYPE)
+        hits = np.ascontiguousarray(hits, abi.HIT_DTYPE)
+        xi = np.ascontiguousarray(rvec_xi, np.float32).reshape(-1, 4)
+        n = len(rays)
+        att, emit = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        out, sc = np.zeros(n, abi.RAY_DTYPE), np.zeros(n, np.int32)
+        _check(lib().srt_shade_kat(self.h, _ptr(rays), _ptr(hits), _ptr(xi), n, _ptr(att), _ptr(emit), _ptr(out), _ptr(sc)))
+        return att, emit, out, sc
+
+    def texture_kat(self, tex, uvp):
+        uvp = np.ascontiguousarray(uvp, np.float32).reshape(-1, 5)
+        out = np.zeros((len(uvp), 3), np.float32)
+        _check(lib().srt_texture_kat(self.h, tex, _ptr(uvp), len(uvp), _ptr(out)))
+        return out

@@ -139,10 +139,21 @@ class Scene:
     # ---- persistence
     def save(self, path):
         d = {k: getattr(self, k) for k in self.ARRAYS}
-        for i, a in self.tex_data.items():
-            d["tex_data_%d" % i] = np.ascontiguousarray(a, np.uint8)
-        d.update(camera=self.camera, cam_args=self.cam_args, render=self.render, background=self.background,
-                 name=np.array(self.name))
+        # identical images (the same PNG loaded by several materials) are stored once
+        blobs, ref = [], np.full(self.tex_kind.shape[0], -1, _I)
+        for i, a in sorted(self.tex_data.items()):
+            a = np.ascontiguousarray(a, np.uint8)
+            for k, b in enumerate(blobs):
+                if b.shape == a.shape and np.array_equal(a, b):
+                    ref[i] = k
+                    break
+            else:
+                ref[i] = len(blobs)
+                blobs.append(a)
+        for k, b in enumerate(blobs):
+            d["tex_blob_%d" % k] = b
+        d.update(tex_blob_ref=ref, camera=self.camera, cam_args=self.cam_args, render=self.render,
+                 background=self.background, name=np.array(self.name))
         np.savez_compressed(path, **d)
 
     @classmethod
@@ -151,9 +162,13 @@ class Scene:
         with np.load(path, allow_pickle=False) as z:
             for k in cls.ARRAYS:
                 setattr(s, k, z[k])
-            for k in z.files:
-                if k.startswith("tex_data_"):
-                    s.tex_data[int(k[9:])] = z[k]
+            ref = z["tex_blob_ref"]
+            blobs = {}
+            for i, k in enumerate(ref):
+                if k >= 0:
+                    if int(k) not in blobs:
+                        blobs[int(k)] = z["tex_blob_%d" % k]
+                    s.tex_data[i] = blobs[int(k)]
             s.camera, s.cam_args, s.render, s.background = z["camera"], z["cam_args"], z["render"], z["background"]
             s.name = str(z["name"])
         return s
