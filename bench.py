@@ -1,0 +1,362 @@
+"""bench.py — BASELINE.json's metric: M path-segments/s (and frame time) of the path-tracing loop.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c4|c3|c2|c1] [--spp S] [--impl reference]
+
+A "step" is one whole frame of the workload (every pixel, all samples).  Default workload = BASELINE config 4:
+main.cpp's Master Chief + PBR-globe scene at 1280x720, 5000 spp, depth 4, the samples of every pixel split
+across the N ranks (strong scaling; one NCCL sum-reduce of the fp32 radiance buffer per frame, resolve on
+rank 0).  One process per GPU; for N > 1 launch under torchrun (see the task contract).
+
+`value`  : whole-job M segments/s with the scene resident in HBM when the timed region starts (device time,
+           CUDA events on the launch stream, max over ranks).
+`e2e`    : the same metric through the host-buffer C-ABI calls a user makes (srt_scene_create from host arrays +
+           render + read-back of the RGBA8 frame), host<->device copies inside the timed region.
+`roofline`, `cpu_baseline`, `clocks`, `gpu_launches`: see DESIGN.md "Measurement".
+
+`--impl reference` times the reference's own CPU code for the same path (oracle/_ref, compiled from
+/root/reference; else the C port) on all host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import multiprocessing as mp
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mpath-segments/s"
+CONFIGS = {  # name -> (scene file, W, H, spp, max_bounce)
+    "c1": ("c1_shirley", 400, 225, 16, 10),
+    "c2": ("c2_cube", 640, 360, 64, 8),
+    "c3": ("c3_masterchief", 426, 240, 1000, 4),
+    "c4": ("c3_masterchief", 1280, 720, 5000, 4),
+}
+WORKLOAD_NAMES = {
+    "c1": "Shirley sphere scene 400x225 16spp depth 10 (BASELINE config 1)",
+    "c2": "cube.gltf+square.gltf 640x360 64spp depth 8 (BASELINE config 2)",
+    "c3": "main.cpp default scene (Master Chief + globe) 426x240 1000spp depth 4 (BASELINE config 3)",
+    "c4": "main.cpp default scene (Master Chief + globe) 1280x720 5000spp depth 4, spp split across GPUs (BASELINE config 4)",
+}
+
+
+def load_workload(args):
+    from sexy_raytracer_b200.scene import Scene
+    name, W, H, spp, depth = CONFIGS[args.config]
+    if args.spp:
+        spp = args.spp
+    s = Scene.load(os.path.join(ROOT, "scenes", name + ".npz"))
+    s.render = np.array([W, H, spp, depth], np.int32)
+    return s, W, H, spp, depth
+
+
+# ---- clocks ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.proc = gpu, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- CPU baseline: the reference's own code on the host cores ----------------------------------------------------
+def _cpu_band(job):
+    """One process = one row band (the reference is single threaded and its RNG is a process-wide static)."""
+    kind, scene_path, W, H, spp, depth, y0, y1, seed = job
+    sys.path.insert(0, ROOT)
+    from oracle import refbind
+    from sexy_raytracer_b200.scene import Scene
+    s = Scene.load(scene_path)
+    if kind == "reference":
+        R = refbind.RefOracle()
+        h = R.from_scene(s)
+        t = time.perf_counter()
+        _, _, seg = R.render(h, s.cam_args, W, H, spp, depth, s.background, y0=y0, y1=y1, seed=seed, want_rgba=False)
+        return seg, time.perf_counter() - t
+    P = refbind.PortOracle()
+    h = P.from_scene(s)
+    t = time.perf_counter()
+    _, st = P.render(h, s, s.render_params(width=W, height=H, spp=spp, max_bounce=depth, seed=seed), y0=y0, y1=y1, nthreads=1)
+    return int(st.segments), time.perf_counter() - t
+
+
+def cpu_frame_sample(args, seconds_per_core=12.0):
+    """A bounded sample of the workload on all host cores: every core renders its own band of rows of the same
+    frame at a reduced spp.  -> (M segments/s, description dict)"""
+    from oracle import refbind
+    kind = "reference" if refbind.RefOracle.available() else "port"
+    name, W, H, spp, depth = CONFIGS[args.config]
+    cores = os.cpu_count() or 1
+    seg_per_spp = W * H * 1.8
+    spp_cpu = int(max(1, min(spp, 64, round(0.33e6 * seconds_per_core * cores / seg_per_spp))))
+    bands = [(kind, os.path.join(ROOT, "scenes", name + ".npz"), W, H, spp_cpu, depth, H * i // cores, H * (i + 1) // cores, 1000 + i)
+             for i in range(cores)]
+    bands = [b for b in bands if b[7] > b[6]]
+    t = time.perf_counter()
+    with mp.get_context("fork").Pool(len(bands)) as pool:
+        res = pool.map(_cpu_band, bands)
+    wall = time.perf_counter() - t
+    seg = sum(r[0] for r in res)
+    slowest = max(r[1] for r in res)
+    return seg / slowest / 1e6, {"kind": kind, "cores": len(bands), "unit": METRIC,
+                                 "sample": "%dx%d frame, all rows, %d spp (of %d), %d row bands = %d processes; %.2f M segments in %.1f s (slowest band)"
+                                 % (W, H, spp_cpu, spp, len(bands), len(bands), seg / 1e6, slowest), "wall_s": round(wall, 2)}
+
+
+# ---- the B200 arm ------------------------------------------------------------------------------------------------
+def algorithmic_bytes_per_segment(c, segments, n_maps=2):
+    """bytes/segment = 32 B + 36 Lt + 40 Ls + 24 A_tri + 3 maps A_tri + 28 (ray), with B, Lt, Ls, A_tri
+    per segment MEASURED by the kernel's own counters on this workload (srt_set_counters)."""
+    B = c["node_visits"] / segments
+    Ls = c["sphere_leaf_tests"] / segments
+    Lt = (c["leaf_tests"] - c["sphere_leaf_tests"]) / segments
+    A = c["triangle_hits"] / segments
+    return 32 * B + 36 * Lt + 40 * Ls + (24 + 3 * n_maps) * A + 28, {"B": B, "Lt": Lt, "Ls": Ls, "A_tri": A}
+
+
+def flops_per_segment(k):
+    """flops/segment = 27 B + 65 Lt + 25 Ls + 175 A_tri + 120 (shade) + 20, un-fused ops"""
+    return 27 * k["B"] + 65 * k["Lt"] + 25 * k["Ls"] + 175 * k["A_tri"] + 120 + 20
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from sexy_raytracer_b200.device import Device
+    from sexy_raytracer_b200.dist import sample_split, reduce_frame
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d needs %d ranks (launch under torch.distributed.run); WORLD_SIZE=%d" % (args.gpus, args.gpus, world))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    scene, W, H, spp, depth = load_workload(args)
+    dev = Device(local)
+    stream = torch.cuda.current_stream()
+    dev.set_stream(stream.cuda_stream)          # library launches + torch events + NCCL on ONE stream
+    ds = dev.upload(scene)
+    begin, count = sample_split(spp, world, rank)
+    P = scene.render_params(width=W, height=H, spp=spp, max_bounce=depth, sample_begin=begin, sample_count=count, seed=2026)
+    accum = torch.zeros(H * W * 3, dtype=torch.float32, device="cuda")
+    rgba = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")    # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        accum.zero_()
+        st = ds.render_accumulate(accum.data_ptr(), P) if count > 0 else None
+        reduce_frame(accum, dst=0)
+        if rank == 0:
+            dev.resolve_dev(accum.data_ptr(), W, H, spp, rgba.data_ptr())
+        return st
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    seg = paths = 0
+    kern_ms = 0.0
+    barrier()
+    for a, b in ev:
+        flush.fill_(1)                           # L2 flush between timed iterations, outside the event pair
+        if world > 1:
+            dist.barrier()
+        a.record(stream)
+        st = step()
+        b.record(stream)
+        if st is not None:
+            seg += int(st.segments); paths += int(st.paths); kern_ms += st.kernel_ms
+    barrier()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    clk = clocks.stop() if rank == 0 else None
+    tot = torch.tensor([float(seg), float(paths)], dtype=torch.float64, device="cuda")
+    tmax = torch.tensor([ms, kern_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    seg_all, paths_all = tot.tolist()
+    ms_all, kern_ms_max = tmax.tolist()
+    value = seg_all / (ms_all * 1e-3) / 1e6
+
+    # ---- e2e: host buffers through the public C-ABI calls, copies inside the timed region
+    h2d = scene.host_bytes()
+    d2h = W * H * 4
+    dev.set_stream(None)
+    e2e_seg = 0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ds2 = dev.upload(scene)                                        # H2D: the flattened scene, every step
+        if world == 1:
+            _, frame, st = ds2.render(P, want_sum=False, want_rgba=True)   # D2H: the RGBA8 frame
+        else:
+            dev.set_stream(stream.cuda_stream)
+            accum.zero_()
+            st = ds2.render_accumulate(accum.data_ptr(), P) if count > 0 else None
+            reduce_frame(accum, dst=0)
+            if rank == 0:
+                dev.resolve_dev(accum.data_ptr(), W, H, spp, rgba.data_ptr())
+                frame = rgba.cpu()
+            dev.set_stream(None)
+        e2e_seg += int(st.segments) if st is not None else 0
+        ds2.close()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    se = torch.tensor([float(e2e_seg)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        dist.all_reduce(se)
+    e2e_value = se.item() / te.item() / 1e6
+
+    line = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel (k_render_mega): counters from a short counted pass of the same frame
+        dev.set_counters(True)
+        stc = ds.render_accumulate(accum.data_ptr(), scene.render_params(width=W, height=H, spp=spp, max_bounce=depth,
+                                                                         sample_begin=0, sample_count=max(1, min(8, spp)), seed=2026))
+        c = dev.last_counters()
+        dev.set_counters(False)
+        bps, k = algorithmic_bytes_per_segment(c, int(stc.segments))
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
+        seg_rank0 = seg / max(1, args.steps)                   # rank 0's segments per launch
+        launch_s = kern_ms / max(1, args.steps) * 1e-3
+        achieved = bps * seg_rank0 / launch_s / 1e9
+        fl = flops_per_segment(k) * seg_rank0 / launch_s / 1e12
+        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+        fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        roofline = {"kernel": "k_render_mega", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak_hbm,
+                    "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "unit": "GB/s",
+                    "frac": round(achieved / peak_hbm, 4), "traffic": None,
+                    "bytes_per_segment": round(bps, 1), "per_segment": {a: round(b, 3) for a, b in k.items()},
+                    "segments_per_launch": seg_rank0, "launch_ms": round(launch_s * 1e3, 3),
+                    "note": "algorithmic bytes are node/primitive fetches; for this scene they are served from shared memory "
+                            "and L1/L2 (whole BVH staged per CTA), so DRAM traffic is far below them - see profiles/",
+                    "fp32": {"achieved_tflops": round(fl, 3), "peak_nominal_tflops": round(fp32_peak, 1),
+                             "frac_fma_peak": round(fl / fp32_peak, 4), "frac_unfused_peak": round(fl / (fp32_peak / 2), 4),
+                             "flops_per_segment": round(flops_per_segment(k), 1)}}
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            v, desc = cpu_frame_sample(args)
+            cpu = dict(value=round(v, 4), **desc)
+        line = {"metric": METRIC, "value": round(value, 2), "unit": "M segments/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": round(ms_all / args.steps, 3), "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD_NAMES[args.config] + (" [spp overridden: %d]" % spp if args.spp else ""),
+                           "width": W, "height": H, "spp": spp, "max_bounce": depth, "parallelism": "spp-split x%d" % world,
+                           "scene": "committed flattening of the reference scene as it loads (globe maps missing upstream -> fallback colour)",
+                           "l2": "256 MiB flush write between timed steps"},
+                "frame_time_s": round(ms_all / args.steps / 1e3, 4), "spp_per_s": round(spp / (ms_all / args.steps / 1e3), 1),
+                "segments_per_step": seg_all / args.steps, "paths_per_step": paths_all / args.steps,
+                "render_kernel_ms_per_step": round(kern_ms_max / args.steps, 3),
+                "e2e": {"value": round(e2e_value, 2), "unit": "M segments/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "s_per_step": round(te.item() / args.steps, 4),
+                        "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out)" if world == 1 else
+                                "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H"},
+                "gpu_launches": args.steps * 2, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}
+    ds.close()
+    dev.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+# ---- the reference arm: the reference's own CPU code, all host cores ----------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    _, W, H, spp, depth = load_workload(args)
+    vals, desc = [], None
+    for i in range(args.warmup + args.steps):
+        v, desc = cpu_frame_sample(args, seconds_per_core=5.0)
+        if i >= args.warmup:
+            vals.append(v)
+    value = sum(vals) / len(vals)
+    cores = desc["cores"]
+    line = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": "M segments/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(desc["wall_s"] * 1e3, 1), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAMES[args.config], "width": W, "height": H, "spp": spp, "max_bounce": depth,
+                       "parallelism": "%d host processes on disjoint row bands (the reference is single threaded)" % cores},
+            "cpu_baseline": dict(value=round(value, 4), **desc),
+            "e2e": {"value": round(value, 4), "unit": "M segments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
+    ap.add_argument("--spp", type=int, default=0, help="override the samples per pixel of the config (not the headline)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

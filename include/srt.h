@@ -231,10 +231,14 @@ const char* srt_status_string(srt_status s);
 const char* srt_last_error(void);
 /* 1 = count node visits / leaf tests in srt_stats (slower kernels); default 0                   */
 srt_status  srt_set_counters(srt_device* dev, int enabled);
-/* node visits, leaf tests and exact (unfiltered) box tests of the last trace/render call          */
-srt_status  srt_last_counters(srt_device* dev, uint64_t* out3);
+/* counters of the last trace/render call: node visits, leaf tests, exact (unfiltered) box tests,
+ * sphere leaf tests, segments that ended on a triangle                                          */
+srt_status  srt_last_counters(srt_device* dev, uint64_t* out5);
 /* the CUDA stream the device launches on (cudaStream_t as void*), for event timing outside      */
 void*       srt_device_stream(srt_device* dev);
+/* launch on the caller's stream instead (e.g. the framework's current stream, so that its events
+ * and NCCL calls order with the render); NULL restores the device's own stream                  */
+srt_status  srt_device_set_stream(srt_device* dev, void* cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -103,6 +103,7 @@ PROTOTYPES = {
     "srt_last_error": (C.c_char_p, []),
     "srt_set_counters": (C.c_int, [_vp, C.c_int]),
     "srt_device_stream": (_vp, [_vp]),
+    "srt_device_set_stream": (C.c_int, [_vp, _vp]),
 }
 
 

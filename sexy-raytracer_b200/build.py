@@ -1,0 +1,35 @@
+"""In-tree build of the CUDA library (sm_100a only) and of the checkers under oracle/."""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libsrt_b200.so")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              # parity contract: no FMA contraction anywhere but the explicit fmaf of the filtered box test;
+              # IEEE division / sqrt and denormals are nvcc's defaults and must stay
+              "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+              "-Xcompiler", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include")]
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_cuda(force=False, verbose=False):
+    srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(ROOT, "include", "srt.h")]
+    if not force and not _stale(LIB, srcs):
+        return LIB
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "srt_b200.cu"), "-o", LIB]
+    subprocess.check_call(cmd)
+    return LIB
+
+
+def build_oracles():
+    """The checkers: plain-C oracle always; the compiled reference only where /root/reference exists."""
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "all"])

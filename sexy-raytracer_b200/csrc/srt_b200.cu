@@ -28,7 +28,8 @@ struct srt_device {
   int gpu = 0;
   int sm_count = 0;
   size_t smem_optin = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;       // the stream kernels are launched on
+  cudaStream_t own_stream = nullptr;   // created by srt_device_create
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   unsigned long long* d_counters = nullptr;   // 8 x u64, see k_render_mega
   int counters = 0;
@@ -73,7 +74,8 @@ srt_status srt_device_create(int gpu_id, srt_device** out) {
   CK(cudaGetDeviceProperties(&prop, gpu_id));
   d->sm_count = prop.multiProcessorCount;
   d->smem_optin = prop.sharedMemPerBlockOptin;
-  CK(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&d->own_stream, cudaStreamNonBlocking));
+  d->stream = d->own_stream;
   CK(cudaEventCreate(&d->ev0));
   CK(cudaEventCreate(&d->ev1));
   CK(cudaMalloc(&d->d_counters, 8 * sizeof(unsigned long long)));
@@ -87,7 +89,7 @@ void srt_device_destroy(srt_device* d) {
   if (d->d_counters) cudaFree(d->d_counters);
   if (d->ev0) cudaEventDestroy(d->ev0);
   if (d->ev1) cudaEventDestroy(d->ev1);
-  if (d->stream) cudaStreamDestroy(d->stream);
+  if (d->own_stream) cudaStreamDestroy(d->own_stream);
   delete d;
 }
 
@@ -97,6 +99,11 @@ srt_status srt_set_counters(srt_device* d, int enabled) {
   return SRT_OK;
 }
 void* srt_device_stream(srt_device* d) { return d ? (void*)d->stream : nullptr; }
+srt_status srt_device_set_stream(srt_device* d, void* cuda_stream) {
+  if (!d) return fail(SRT_ERR_INVALID, "device is NULL");
+  d->stream = cuda_stream ? (cudaStream_t)cuda_stream : d->own_stream;
+  return SRT_OK;
+}
 
 }  // extern "C"
 

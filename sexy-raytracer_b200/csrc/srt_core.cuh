@@ -195,7 +195,7 @@ __device__ __forceinline__ bool sph_hit(const Sph* __restrict__ sphs, int j, con
   return true;
 }
 
-struct Counters { unsigned long long nodes, leaves, exact; };
+struct Counters { unsigned long long nodes, leaves, exact, sph_leaves, tri_hits; };
 
 // hittableList::hit -> bvhNode::hit (hittablelist.h:33-47, bvh.h:97-105) in the threaded form.
 // Rule: walk in pre-order; one running tCur = t of the most recently ACCEPTED leaf
@@ -222,7 +222,7 @@ __device__ __forceinline__ void traverse(const Scene& sc, const Node* nodes, con
         for (int k = 0; k < 2; k++) {
           int p = k == 0 ? w6 : w7;
           if (p < 0) break;
-          if (COUNT) ++cnt->leaves;
+          if (COUNT) { ++cnt->leaves; if (p >= sc.n_tri) ++cnt->sph_leaves; }
           float t;
           bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, tMin, t) : sph_hit(sc.sphs, p - sc.n_tri, r, tMin, tCur, t);
           if (acc) { tCur = t; prim = p; }

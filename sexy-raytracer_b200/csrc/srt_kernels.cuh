@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(Scene sc, int nodes_in_smem,
                                                     unsigned long long* counters) {
   extern __shared__ float4 smem_nodes[];
   const Node* nodes = stage_nodes(sc, nodes_in_smem != 0, smem_nodes);
-  Counters cnt = {0, 0, 0};
+  Counters cnt = {0, 0, 0, 0, 0};
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     Ray r = load_ray(&rays[i]);
     int prim; float t;
@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(Scene sc, int nodes_in_smem,
   }
   if (COUNT) {
     atomicAdd(&counters[2], cnt.nodes); atomicAdd(&counters[3], cnt.leaves); atomicAdd(&counters[4], cnt.exact);
+    atomicAdd(&counters[6], cnt.sph_leaves);
   }
 }
 
@@ -98,7 +99,8 @@ __device__ __forceinline__ Ray generate_ray(const RenderArgs& A, int x, int y, u
 // ended regenerates the next sample of its pixel in the same iteration, so the warp stays full until
 // the unit runs dry (no queues, no atomics on the hot path).  rayColor's recursion (main.cpp:33-52)
 //   L = e0 + a0*(e1 + a1*(e2 + ...))   becomes   L += thr*e_k ; thr *= a_k.
-// counters: [0] paths, [1] segments, [2] node visits, [3] leaf tests, [4] exact box tests, [5] unit cursor
+// counters: [0] paths, [1] segments, [2] node visits, [3] leaf tests, [4] exact box tests, [5] unit cursor,
+//           [6] sphere leaf tests, [7] segments that ended on a triangle
 template <bool COUNT>
 __global__ void __launch_bounds__(512, 1) k_render_mega(Scene sc, int nodes_in_smem, RenderArgs A, float* __restrict__ accum,
                                                         unsigned long long* counters) {
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(512, 1) k_render_mega(Scene sc, int nodes_in_s
   const Node* nodes = stage_nodes(sc, nodes_in_smem != 0, smem_nodes);
   const int lane = threadIdx.x & 31;
   unsigned long long n_paths = 0, n_segments = 0;
-  Counters cnt = {0, 0, 0};
+  Counters cnt = {0, 0, 0, 0, 0};
 
   for (;;) {
     long long unit = 0;
@@ -141,6 +143,7 @@ __global__ void __launch_bounds__(512, 1) k_render_mega(Scene sc, int nodes_in_s
         L = mk(L.x + thr.x * A.bg[0], L.y + thr.y * A.bg[1], L.z + thr.z * A.bg[2]);
         done = true;
       } else {
+        if (COUNT && prim < sc.n_tri) ++cnt.tri_hits;
         const int mat_id = prim < sc.n_tri ? __float_as_int(__ldg(&sc.tris[prim].d.y))
                                            : __float_as_int(__ldg(&sc.sphs[prim - sc.n_tri].c.y));
         const Mat m = sc.mats[mat_id];
@@ -183,11 +186,16 @@ __global__ void __launch_bounds__(512, 1) k_render_mega(Scene sc, int nodes_in_s
       cnt.nodes += __shfl_down_sync(0xffffffffu, cnt.nodes, o);
       cnt.leaves += __shfl_down_sync(0xffffffffu, cnt.leaves, o);
       cnt.exact += __shfl_down_sync(0xffffffffu, cnt.exact, o);
+      cnt.sph_leaves += __shfl_down_sync(0xffffffffu, cnt.sph_leaves, o);
+      cnt.tri_hits += __shfl_down_sync(0xffffffffu, cnt.tri_hits, o);
     }
   }
   if (lane == 0) {
     atomicAdd(&counters[0], n_paths); atomicAdd(&counters[1], n_segments);
-    if (COUNT) { atomicAdd(&counters[2], cnt.nodes); atomicAdd(&counters[3], cnt.leaves); atomicAdd(&counters[4], cnt.exact); }
+    if (COUNT) {
+      atomicAdd(&counters[2], cnt.nodes); atomicAdd(&counters[3], cnt.leaves); atomicAdd(&counters[4], cnt.exact);
+      atomicAdd(&counters[6], cnt.sph_leaves); atomicAdd(&counters[7], cnt.tri_hits);
+    }
   }
 }
 

@@ -155,13 +155,15 @@ srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_
   return SRT_OK;
 }
 
-// node visits / leaf tests / exact (unfiltered) box tests of the last srt_trace_rays or render call
-srt_status srt_last_counters(srt_device* dev, uint64_t* out3) {
-  if (!dev || !out3) return fail(SRT_ERR_INVALID, "NULL argument");
+// counters of the last srt_trace_rays or render call (only with srt_set_counters(dev, 1)):
+// node visits, leaf tests, exact (unfiltered) box tests, sphere leaf tests, segments ending on a triangle
+srt_status srt_last_counters(srt_device* dev, uint64_t* out5) {
+  uint64_t* out3 = out5;
+  if (!dev || !out5) return fail(SRT_ERR_INVALID, "NULL argument");
   unsigned long long h[8];
   CK(cudaSetDevice(dev->gpu));
   CK(cudaMemcpy(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost));
-  out3[0] = h[2]; out3[1] = h[3]; out3[2] = h[4];
+  out3[0] = h[2]; out3[1] = h[3]; out3[2] = h[4]; out3[3] = h[6]; out3[4] = h[7];
   return SRT_OK;
 }
 

@@ -55,13 +55,18 @@ class Device:
         _check(lib().srt_set_counters(self.h, 1 if on else 0))
 
     def last_counters(self):
-        out = np.zeros(3, np.uint64)
+        out = np.zeros(5, np.uint64)
         _check(lib().srt_last_counters(self.h, _ptr(out)))
-        return {"node_visits": int(out[0]), "leaf_tests": int(out[1]), "exact_box_tests": int(out[2])}
+        return {"node_visits": int(out[0]), "leaf_tests": int(out[1]), "exact_box_tests": int(out[2]),
+                "sphere_leaf_tests": int(out[3]), "triangle_hits": int(out[4])}
 
     @property
     def stream(self):
         return lib().srt_device_stream(self.h)
+
+    def set_stream(self, cuda_stream_ptr):
+        """Launch on the caller's CUDA stream (an int / void*; None restores the device's own stream)."""
+        _check(lib().srt_device_set_stream(self.h, cuda_stream_ptr))
 
     def upload(self, scene):
         return DeviceScene(self, scene)
