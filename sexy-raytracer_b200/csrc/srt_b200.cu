@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "srt_kernels.cuh"
+#include "srt_phased.cuh"
 
 using namespace srt;
 

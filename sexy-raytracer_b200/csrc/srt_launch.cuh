@@ -10,14 +10,23 @@ struct DevBuf {   // scoped device allocation
   template <typename T> T* as() { return static_cast<T*>(p); }
 };
 
-struct RenderPlan { RenderArgs A; int blocks, threads; size_t smem; };
+struct RenderPlan { RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn; };
+
+// variant 1: k_render_mega (flat per-lane loop); variant 3: k_render_phased (warp-voted phases); 0 = auto = 3
+typedef void (*phased_fn)(Scene, RenderArgs, PhaseTune, float*, unsigned long long*);
+template <int THREADS>
+phased_fn pick_phased(bool count, bool smem) {
+  if (count) return smem ? k_render_phased<true, true, THREADS> : k_render_phased<true, false, THREADS>;
+  return smem ? k_render_phased<false, true, THREADS> : k_render_phased<false, false, THREADS>;
+}
 
 srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_params* P, RenderPlan& plan) {
   if (!s || !cam || !P) return fail(SRT_ERR_INVALID, "NULL argument");
   if (P->width < 2 || P->height < 2) return fail(SRT_ERR_INVALID, "width and height must be >= 2 (main.cpp:210-211 divide by W-1, H-1)");
   if ((int64_t)P->width * P->height > (int64_t)INT32_MAX / 4) return fail(SRT_ERR_UNSUPPORTED, "frame too large");
   if (P->spp <= 0 || P->max_bounce < 0 || P->sample_begin < 0 || P->sample_count < 0) return fail(SRT_ERR_INVALID, "bad sample/bounce counts");
-  if (P->variant != 0 && P->variant != 1) return fail(SRT_ERR_UNSUPPORTED, "render variant not built (1 = megakernel)");
+  if (P->variant != 0 && P->variant != 1 && P->variant != 3)
+    return fail(SRT_ERR_UNSUPPORTED, "render variant not built (1 = flat megakernel, 3 = phased megakernel; 2 = wavefront is not)");
   RenderArgs& A = plan.A;
   A.cam = *cam; A.W = P->width; A.H = P->height;
   A.sample_begin = P->sample_begin; A.sample_count = P->sample_count > 0 ? P->sample_count : P->spp;
@@ -30,9 +39,27 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   srt_device* dev = s->dev;
   plan.threads = 512;
   plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
+  plan.variant = P->variant ? P->variant : 3;
+  plan.tune = PhaseTune{16, 12, 20};
+  plan.fn = nullptr;
   int per_sm = 0;
   cudaError_t e;
-  if (dev->counters) {
+  if (plan.variant == 3) {
+    // SRT_TUNE="threads,th_shade,th_leaf,th_trav" (tuning sweeps only; results do not depend on it)
+    if (const char* t = getenv("SRT_TUNE")) {
+      int a = 0, b = 0, c = 0, d = 0;
+      if (sscanf(t, "%d,%d,%d,%d", &a, &b, &c, &d) == 4 && (a == 256 || a == 512 || a == 768 || a == 1024) && b >= 1 && c >= 1 && d >= 1) {
+        plan.threads = a; plan.tune = PhaseTune{b, c, d};
+      }
+    }
+    phased_fn fn = plan.threads == 1024 ? pick_phased<1024>(dev->counters, s->nodes_in_smem)
+                   : plan.threads == 768 ? pick_phased<768>(dev->counters, s->nodes_in_smem)
+                   : plan.threads == 256 ? pick_phased<256>(dev->counters, s->nodes_in_smem)
+                                         : pick_phased<512>(dev->counters, s->nodes_in_smem);
+    plan.fn = (const void*)fn;
+    e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
+  } else if (dev->counters) {
     e = cudaFuncSetAttribute(k_render_mega<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render_mega<true>, plan.threads, plan.smem);
   } else {
@@ -61,7 +88,11 @@ srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, sr
   srt_device* dev = s->dev;
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaEventRecord(dev->ev0, dev->stream));
-  if (dev->counters)
+  if (plan.variant == 3) {
+    Scene sc = s->sc; RenderArgs A = plan.A; PhaseTune tune = plan.tune; unsigned long long* ctr = dev->d_counters;
+    void* args[] = {&sc, &A, &tune, &accum_dev, &ctr};
+    CK(cudaLaunchKernel(plan.fn, dim3(plan.blocks), dim3(plan.threads), args, plan.smem, dev->stream));
+  } else if (dev->counters)
     k_render_mega<true><<<plan.blocks, plan.threads, plan.smem, dev->stream>>>(s->sc, s->nodes_in_smem, plan.A, accum_dev, dev->d_counters);
   else
     k_render_mega<false><<<plan.blocks, plan.threads, plan.smem, dev->stream>>>(s->sc, s->nodes_in_smem, plan.A, accum_dev, dev->d_counters);

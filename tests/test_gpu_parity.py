@@ -238,6 +238,30 @@ def test_sample_split_is_additive(dev_scenes, scenes):
     assert np.abs(again[fin] - full[fin]).max() <= 1e-4 * max(1.0, np.abs(full[fin]).max())
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_variants_agree(name, device, dev_scenes, scenes):
+    """k_render_phased (variant 3, warp-voted phases) only re-schedules lanes: same Philox stream, same per-lane
+    sample order => the fp32 sums are BIT-identical to k_render_mega (variant 1), counters included."""
+    s = scenes[name]
+    W, H, spp = SMALL[name]
+    kw = dict(width=W, height=H, spp=spp, seed=11)
+    a, ra, sa = dev_scenes[name].render(s.render_params(variant=1, **kw))
+    b, rb, sb = dev_scenes[name].render(s.render_params(variant=3, **kw))
+    assert sa.paths == sb.paths and sa.segments == sb.segments
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+    assert (ra == rb).all()
+    device.set_counters(True)
+    try:
+        _, _, ca = dev_scenes[name].render(s.render_params(variant=1, **kw), want_rgba=False)
+        k1 = device.last_counters()
+        _, _, cb = dev_scenes[name].render(s.render_params(variant=3, **kw), want_rgba=False)
+        k3 = device.last_counters()
+    finally:
+        device.set_counters(False)
+    assert ca.node_visits == cb.node_visits and ca.leaf_tests == cb.leaf_tests
+    assert k1["sphere_leaf_tests"] == k3["sphere_leaf_tests"] and k1["triangle_hits"] == k3["triangle_hits"]
+
+
 def test_full_size_properties(dev_scenes, scenes):
     """BASELINE config 4 geometry (1280x720) at reduced spp: every pixel written, counters consistent."""
     s = scenes["c3_masterchief"]
