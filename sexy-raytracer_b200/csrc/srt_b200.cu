@@ -10,6 +10,7 @@
 
 #include "srt_kernels.cuh"
 #include "srt_phased.cuh"
+#include "srt_wavefront.cuh"
 
 using namespace srt;
 
@@ -34,7 +35,14 @@ struct srt_device {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   unsigned long long* d_counters = nullptr;   // 8 x u64, see k_render_mega
   int counters = 0;
+  // wavefront variant: path-slot pool (grown on demand), cursors, pinned read-back ring
+  WfPool wf{};
+  size_t wf_capacity = 0;
+  WfCursors* d_wf_cur = nullptr;
+  WfCursors* h_wf_ring = nullptr;             // pinned, WF_RING entries
+  cudaEvent_t wf_ev[8] = {};
 };
+static const int WF_RING = 8;
 
 struct srt_scene {
   srt_device* dev = nullptr;
@@ -88,6 +96,10 @@ void srt_device_destroy(srt_device* d) {
   if (!d) return;
   cudaSetDevice(d->gpu);
   if (d->d_counters) cudaFree(d->d_counters);
+  if (d->wf.ray_o) cudaFree(d->wf.ray_o);
+  if (d->d_wf_cur) cudaFree(d->d_wf_cur);
+  if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
+  for (int k = 0; k < WF_RING; k++) if (d->wf_ev[k]) cudaEventDestroy(d->wf_ev[k]);
   if (d->ev0) cudaEventDestroy(d->ev0);
   if (d->ev1) cudaEventDestroy(d->ev1);
   if (d->own_stream) cudaStreamDestroy(d->own_stream);

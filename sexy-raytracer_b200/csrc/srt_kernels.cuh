@@ -94,6 +94,40 @@ __device__ __forceinline__ Ray generate_ray(const RenderArgs& A, int x, int y, u
   return camera_get_ray(A.cam, u, v, dx, dy, u01(c.x));
 }
 
+// One finished segment of a path: main.cpp:39-51 after world.hit returned (prim, t).  Updates the path's
+// radiance L and throughput thr (rayColor's recursion L = e0 + a0*(e1 + a1*(...)) unrolled), replaces r by
+// the scattered ray and advances bounce.  Returns true when the path ends here.
+template <bool COUNT>
+__device__ __forceinline__ bool shade_segment(const Scene& sc, const RenderArgs& A, uint32_t pixel, uint32_t sample, int& bounce,
+                                              Ray& r, int prim, float t, V3& L, V3& thr, Counters& cnt) {
+  if (prim < 0) {                                                         // miss -> background, main.cpp:39-40
+    L = mk(L.x + thr.x * A.bg[0], L.y + thr.y * A.bg[1], L.z + thr.z * A.bg[2]);
+    return true;
+  }
+  if (COUNT && prim < sc.n_tri) ++cnt.tri_hits;
+  const int mat_id = prim < sc.n_tri ? __float_as_int(__ldg(&sc.tris[prim].d.y))
+                                     : __float_as_int(__ldg(&sc.sphs[prim - sc.n_tri].c.y));
+  const Mat m = sc.mats[mat_id];
+  Rec rec;
+  finish_hit(sc, prim, r, t, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
+  const uint4 x4 = philox(A.seed, pixel, sample, 2u + (uint32_t)bounce);
+  V3 rvec = mk(0, 0, 0);
+  if (m.kind == SRT_MAT_PBR) rvec = sample_unit_vector(u01(x4.x), u01(x4.y));
+  else if (m.kind == SRT_MAT_METAL) rvec = sample_unit_ball(u01(x4.x), u01(x4.y), u01(x4.z));
+  V3 e = material_emitted(sc, m, rec);
+  L = mk(L.x + thr.x * e.x, L.y + thr.y * e.y, L.z + thr.z * e.z);
+  V3 att; Ray next;
+  if (!material_scatter(sc, m, r, rec, rvec, u01(x4.z), att, next)) return true;
+  thr = mk(thr.x * att.x, thr.y * att.y, thr.z * att.z);
+  if (A.rr_begin > 0 && bounce + 1 >= A.rr_begin) {     // Russian roulette: not in the reference, off by default
+    float q = fminf(fmaxf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), 0.05f), 1.0f);
+    if (!(u01(x4.w) < q)) return true;
+    float inv = 1.0f / q; thr = mk(thr.x * inv, thr.y * inv, thr.z * inv);
+  }
+  r = next;
+  return ++bounce >= A.max_bounce;                       // maxBounce <= 0 -> (0,0,0), main.cpp:36-37
+}
+
 // Persistent megakernel.  A warp owns one work unit at a time = (8x4 pixel tile, chunk of samples);
 // lane l owns pixel l of the tile.  The body is ONE flat loop over path segments: a lane whose path
 // ended regenerates the next sample of its pixel in the same iteration, so the warp stays full until
@@ -138,38 +172,7 @@ __global__ void __launch_bounds__(512, 1) k_render_mega(Scene sc, int nodes_in_s
       ++n_segments;
       int prim; float t;
       traverse<COUNT>(sc, nodes, r, 0.001f, __int_as_float(0x7f800000), prim, t, &cnt);
-      bool done;
-      if (prim < 0) {
-        L = mk(L.x + thr.x * A.bg[0], L.y + thr.y * A.bg[1], L.z + thr.z * A.bg[2]);
-        done = true;
-      } else {
-        if (COUNT && prim < sc.n_tri) ++cnt.tri_hits;
-        const int mat_id = prim < sc.n_tri ? __float_as_int(__ldg(&sc.tris[prim].d.y))
-                                           : __float_as_int(__ldg(&sc.sphs[prim - sc.n_tri].c.y));
-        const Mat m = sc.mats[mat_id];
-        Rec rec;
-        finish_hit(sc, prim, r, t, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
-        const uint4 x4 = philox(A.seed, pixel, sample, 2u + (uint32_t)bounce);
-        V3 rvec = mk(0, 0, 0);
-        if (m.kind == SRT_MAT_PBR) rvec = sample_unit_vector(u01(x4.x), u01(x4.y));
-        else if (m.kind == SRT_MAT_METAL) rvec = sample_unit_ball(u01(x4.x), u01(x4.y), u01(x4.z));
-        V3 e = material_emitted(sc, m, rec);
-        L = mk(L.x + thr.x * e.x, L.y + thr.y * e.y, L.z + thr.z * e.z);
-        V3 att; Ray next;
-        if (!material_scatter(sc, m, r, rec, rvec, u01(x4.z), att, next)) {
-          done = true;
-        } else {
-          thr = mk(thr.x * att.x, thr.y * att.y, thr.z * att.z);
-          done = false;
-          if (A.rr_begin > 0 && bounce + 1 >= A.rr_begin) {     // Russian roulette: not in the reference, off by default
-            float q = fminf(fmaxf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), 0.05f), 1.0f);
-            if (!(u01(x4.w) < q)) done = true;
-            else { float inv = 1.0f / q; thr = mk(thr.x * inv, thr.y * inv, thr.z * inv); }
-          }
-          r = next;
-          if (++bounce >= A.max_bounce) done = true;            // maxBounce <= 0 -> (0,0,0), main.cpp:36-37
-        }
-      }
+      const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, prim, t, L, thr, cnt);
       if (done) { sum = sum + L; bounce = -1; }
     }
     if (valid) {

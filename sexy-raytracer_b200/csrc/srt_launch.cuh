@@ -10,7 +10,17 @@ struct DevBuf {   // scoped device allocation
   template <typename T> T* as() { return static_cast<T*>(p); }
 };
 
-struct RenderPlan { RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn; };
+struct RenderPlan {
+  RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
+  int wf_slots, wf_th_walk; const void* wf_shade;     // variant 2
+};
+
+typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
+template <int THREADS>
+extend_fn pick_extend(bool count, bool smem) {
+  if (count) return smem ? k_wf_extend<true, true, THREADS> : k_wf_extend<true, false, THREADS>;
+  return smem ? k_wf_extend<false, true, THREADS> : k_wf_extend<false, false, THREADS>;
+}
 
 // variant 1: k_render_mega (flat per-lane loop); variant 3: k_render_phased (warp-voted phases); 0 = auto = 3
 typedef void (*phased_fn)(Scene, RenderArgs, PhaseTune, float*, unsigned long long*);
@@ -25,8 +35,7 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   if (P->width < 2 || P->height < 2) return fail(SRT_ERR_INVALID, "width and height must be >= 2 (main.cpp:210-211 divide by W-1, H-1)");
   if ((int64_t)P->width * P->height > (int64_t)INT32_MAX / 4) return fail(SRT_ERR_UNSUPPORTED, "frame too large");
   if (P->spp <= 0 || P->max_bounce < 0 || P->sample_begin < 0 || P->sample_count < 0) return fail(SRT_ERR_INVALID, "bad sample/bounce counts");
-  if (P->variant != 0 && P->variant != 1 && P->variant != 3)
-    return fail(SRT_ERR_UNSUPPORTED, "render variant not built (1 = flat megakernel, 3 = phased megakernel; 2 = wavefront is not)");
+  if (P->variant < 0 || P->variant > 3) return fail(SRT_ERR_INVALID, "render variant must be 0 (auto), 1, 2 or 3");
   RenderArgs& A = plan.A;
   A.cam = *cam; A.W = P->width; A.H = P->height;
   A.sample_begin = P->sample_begin; A.sample_count = P->sample_count > 0 ? P->sample_count : P->spp;
@@ -44,7 +53,26 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   plan.fn = nullptr;
   int per_sm = 0;
   cudaError_t e;
-  if (plan.variant == 3) {
+  if (plan.variant == 2) {
+    // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
+    plan.wf_slots = 1 << 21; plan.threads = 1024; plan.wf_th_walk = 20;
+    if (const char* t = getenv("SRT_WF")) {
+      int a = 0, b = 0, c = 0;
+      if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
+        plan.wf_slots = a; plan.threads = b; plan.wf_th_walk = c;
+      }
+    }
+    const long long total = (long long)A.n_tiles * 32 * A.sample_count;
+    if ((long long)plan.wf_slots > total) plan.wf_slots = (int)((total + 255) / 256 * 256);
+    extend_fn fn = plan.threads == 1024 ? pick_extend<1024>(dev->counters, s->nodes_in_smem)
+                   : plan.threads == 768 ? pick_extend<768>(dev->counters, s->nodes_in_smem)
+                   : plan.threads == 256 ? pick_extend<256>(dev->counters, s->nodes_in_smem)
+                                         : pick_extend<512>(dev->counters, s->nodes_in_smem);
+    plan.fn = (const void*)fn;
+    plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
+    e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
+  } else if (plan.variant == 3) {
     // SRT_TUNE="threads,th_shade,th_leaf,th_trav" (tuning sweeps only; results do not depend on it)
     if (const char* t = getenv("SRT_TUNE")) {
       int a = 0, b = 0, c = 0, d = 0;
@@ -84,8 +112,80 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   return SRT_OK;
 }
 
+// variant 2: SHADE(+regenerate) / EXTEND waves over the slot pool until the frame's paths are used up
+srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
+  srt_device* dev = s->dev;
+  const size_t per_slot = 2 * sizeof(float4) + sizeof(int2) + sizeof(uint2) + 2 * sizeof(float4);
+  const size_t N = (size_t)plan.wf_slots;
+  if (dev->wf_capacity < N) {
+    if (dev->wf.ray_o) { CK(cudaFree(dev->wf.ray_o)); dev->wf.ray_o = nullptr; dev->wf_capacity = 0; }
+    void* base = nullptr;
+    cudaError_t e = cudaMalloc(&base, N * per_slot);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_NOMEM, "wavefront slot pool: " + std::string(cudaGetErrorString(e))); }
+    dev->wf.ray_o = (float4*)base;
+    dev->wf_capacity = N;
+  }
+  if (!dev->d_wf_cur) {
+    CK(cudaMalloc(&dev->d_wf_cur, sizeof(WfCursors)));
+    CK(cudaMallocHost(&dev->h_wf_ring, WF_RING * sizeof(WfCursors)));
+    for (int k = 0; k < WF_RING; k++) CK(cudaEventCreateWithFlags(&dev->wf_ev[k], cudaEventDisableTiming));
+  }
+  WfPool pool = dev->wf;
+  {  // carve the SoA arrays out of the one allocation (capacity-strided so the layout survives smaller frames)
+    char* b = (char*)dev->wf.ray_o; const size_t C = dev->wf_capacity;
+    pool.ray_o = (float4*)b; b += C * sizeof(float4);
+    pool.ray_d = (float4*)b; b += C * sizeof(float4);
+    pool.thr = (float4*)b;   b += C * sizeof(float4);
+    pool.rad = (float4*)b;   b += C * sizeof(float4);
+    pool.hit = (int2*)b;     b += C * sizeof(int2);
+    pool.id = (uint2*)b;
+    pool.n_slots = (int)N;
+  }
+  const unsigned long long total = (unsigned long long)plan.A.n_tiles * 32ull * (unsigned long long)plan.A.sample_count;
+  Scene sc = s->sc; RenderArgs A = plan.A; WfCursors* cur = dev->d_wf_cur; unsigned long long* ctr = dev->d_counters;
+  int th_walk = plan.wf_th_walk;
+  void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
+  void* extend_args[] = {&sc, &pool, &cur, &th_walk, &ctr};
+  const unsigned shade_blocks = (unsigned)((N + 255) / 256);
+  int launches = 0;
+
+  CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
+  CK(cudaMemsetAsync(cur, 0, sizeof(WfCursors), dev->stream));
+  CK(cudaEventRecord(dev->ev0, dev->stream));
+  k_wf_reset<<<shade_blocks, 256, 0, dev->stream>>>(pool);
+  ++launches;
+  // The host learns (alive, path cursor) of wave j when it is about to launch wave j + LAG: the queue never drains,
+  // and at most LAG empty waves run after the frame is finished.
+  const int LAG = 4;
+  for (long long j = 0;; j++) {
+    if (j >= LAG) {
+      const int slot = (int)((j - LAG) % WF_RING);
+      CK(cudaEventSynchronize(dev->wf_ev[slot]));
+      const WfCursors& c = dev->h_wf_ring[slot];
+      if (c.alive == 0 && c.path >= total) break;
+    }
+    CK(cudaLaunchKernel(plan.wf_shade, dim3(shade_blocks), dim3(256), shade_args, 0, dev->stream));
+    CK(cudaMemcpyAsync(&dev->h_wf_ring[j % WF_RING], cur, sizeof(WfCursors), cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaEventRecord(dev->wf_ev[j % WF_RING], dev->stream));
+    CK(cudaLaunchKernel(plan.fn, dim3(plan.blocks), dim3(plan.threads), extend_args, plan.smem, dev->stream));
+    launches += 2;
+  }
+  CK(cudaEventRecord(dev->ev1, dev->stream));
+  unsigned long long h[8];
+  CK(cudaMemcpyAsync(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->paths = h[0]; stats->segments = h[1]; stats->node_visits = h[2]; stats->leaf_tests = h[3];
+    float ms = 0; CK(cudaEventElapsedTime(&ms, dev->ev0, dev->ev1));
+    stats->kernel_ms = ms; stats->launches = launches;
+  }
+  return SRT_OK;
+}
+
 srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
   srt_device* dev = s->dev;
+  if (plan.variant == 2) return run_wavefront(s, plan, accum_dev, stats);
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaEventRecord(dev->ev0, dev->stream));
   if (plan.variant == 3) {

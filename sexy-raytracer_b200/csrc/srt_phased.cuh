@@ -73,34 +73,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_render_phased(Scene sc, RenderAr
         if (stF) {
           bool done = true;
           if (bounce >= 0) {
-            if (prim < 0) {
-              L = mk(L.x + thr.x * A.bg[0], L.y + thr.y * A.bg[1], L.z + thr.z * A.bg[2]);   // main.cpp:39-40
-            } else {
-              if (COUNT && prim < sc.n_tri) ++cnt.tri_hits;
-              const int mat_id = prim < sc.n_tri ? __float_as_int(__ldg(&sc.tris[prim].d.y))
-                                                 : __float_as_int(__ldg(&sc.sphs[prim - sc.n_tri].c.y));
-              const Mat m = sc.mats[mat_id];
-              Rec rec;
-              finish_hit(sc, prim, r, tCur, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
-              const uint4 x4 = philox(A.seed, pixel, sample, 2u + (uint32_t)bounce);
-              V3 rvec = mk(0, 0, 0);
-              if (m.kind == SRT_MAT_PBR) rvec = sample_unit_vector(u01(x4.x), u01(x4.y));
-              else if (m.kind == SRT_MAT_METAL) rvec = sample_unit_ball(u01(x4.x), u01(x4.y), u01(x4.z));
-              V3 e = material_emitted(sc, m, rec);
-              L = mk(L.x + thr.x * e.x, L.y + thr.y * e.y, L.z + thr.z * e.z);
-              V3 att; Ray next;
-              if (material_scatter(sc, m, r, rec, rvec, u01(x4.z), att, next)) {
-                thr = mk(thr.x * att.x, thr.y * att.y, thr.z * att.z);
-                done = false;
-                if (A.rr_begin > 0 && bounce + 1 >= A.rr_begin) {   // Russian roulette: not in the reference, off by default
-                  float q = fminf(fmaxf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), 0.05f), 1.0f);
-                  if (!(u01(x4.w) < q)) done = true;
-                  else { float inv = 1.0f / q; thr = mk(thr.x * inv, thr.y * inv, thr.z * inv); }
-                }
-                r = next;
-                if (++bounce >= A.max_bounce) done = true;          // maxBounce <= 0 -> (0,0,0), main.cpp:36-37
-              }
-            }
+            done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, prim, tCur, L, thr, cnt);
             if (done) { sum = sum + L; bounce = -1; }
           }
           if (done && s < s_end) {                                  // next sample of this lane's pixel

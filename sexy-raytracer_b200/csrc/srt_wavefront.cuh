@@ -1,0 +1,232 @@
+// srt_wavefront.cuh — variant 2: the frame as alternating EXTEND / SHADE kernels over a pool of path slots.
+//
+// Why (profiles/r1_v1_megakernel_summary.md, profiles/r1_v3_phased_summary.md): in the megakernels a lane
+// that finished its traversal must wait for shading code (~450 instructions + ray generation) that the
+// rest of its warp does not need, and leaf tests run with 2-3 lanes.  Here
+//   k_wf_extend : ONLY hittableList::hit (bvh.h:97-105 + leaf tests).  Persistent warps; a lane whose ray
+//                 is finished stores (prim, t) and fetches the next ray of the pool (warp-aggregated
+//                 atomic), so the warp never waits for a long ray; leaf tests are batched by a warp vote.
+//   k_wf_shade  : main.cpp:44-51 for every slot with all lanes active, then path regeneration
+//                 (main.cpp:204-217): a slot whose path ended adds its radiance to the pixel
+//                 (red.global.add.f32) and takes the next (pixel, sample) of the frame from a global cursor.
+// Path state lives in HBM between the two (SoA, ~190 B of traffic per segment — two orders of magnitude
+// below what 6.5 TB/s allows at this path's segment rates).  Traversal order per ray, arithmetic and the
+// Philox keying (pixel, sample, bounce) are the megakernel's: frames agree up to fp32 summation order
+// of a pixel's samples.
+#pragma once
+#include "srt_phased.cuh"
+
+namespace srt {
+
+struct WfPool {
+  float4* ray_o;      // (o.xyz, time)
+  float4* ray_d;      // (d.xyz, active flag as int bits: 1 = a segment is waiting to be traced)
+  int2*   hit;        // (prim, t bits) written by extend
+  uint2*  id;         // (pixel, sample)
+  float4* thr;        // (throughput.xyz, bounce as int bits; bounce < 0 = slot has no path)
+  float4* rad;        // (radiance so far .xyz, -)
+  int     n_slots;
+};
+
+// cursors (device memory, zeroed per frame): [0] next path id, [1] extend ray cursor (zeroed per wave),
+// [2] slots still alive after the last shade, [3] unused
+struct WfCursors { unsigned long long path, ray, alive, pad; };
+
+// ---- EXTEND ------------------------------------------------------------------------------------------
+template <bool COUNT, bool SMEM, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
+                                                          unsigned long long* counters) {
+  extern __shared__ float4 smem_nodes[];
+  const Node* nodes = stage_nodes(sc, SMEM, smem_nodes);
+  const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  const int n = sc.n_nodes;
+  const float INF = __int_as_float(0x7f800000);
+  Counters cnt = {0, 0, 0, 0, 0};
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // counted anew by the next shade pass
+
+  Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
+  RayAux aux = make_aux(r, 0);
+  int slot = -1;                   // -1: this lane holds no ray
+  int i = n, pend0 = -1, pend1 = -1, prim = -1;
+  float tCur = INF;
+  bool pool_dry = false;           // warp-uniform: the wave's rays are all handed out
+
+  for (;;) {
+    // ---- service phase 1: leaf tests of pending primitives, in reference order
+    if (pend0 >= 0) {
+#pragma unroll 1
+      for (int k = 0; k < 2; k++) {
+        const int p = k == 0 ? pend0 : pend1;
+        if (p < 0) break;
+        if (COUNT) { ++cnt.leaves; if (p >= sc.n_tri) ++cnt.sph_leaves; }
+        float t;
+        const bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
+        if (acc) { tCur = t; prim = p; }
+      }
+      pend0 = pend1 = -1;
+    }
+    // ---- service phase 2: finished rays store their hit
+    if (slot >= 0 && i >= n && pend0 < 0) {
+      pool.hit[slot] = make_int2(prim, __float_as_int(tCur));
+      slot = -1;
+    }
+    // ---- service phase 3: idle lanes fetch the next rays of the wave (one atomic per warp)
+    if (!pool_dry) {
+      const unsigned need = __ballot_sync(FULL, slot < 0);
+      if (need) {
+        unsigned long long base = 0;
+        const int leader = __ffs(need) - 1;
+        if (lane == leader) base = atomicAdd(&cur->ray, (unsigned long long)__popc(need));
+        base = __shfl_sync(FULL, base, leader);
+        if (base + __popc(need) >= (unsigned long long)pool.n_slots) pool_dry = true;
+        if (slot < 0) {
+          const unsigned long long mine = base + __popc(need & ((1u << lane) - 1));
+          if (mine < (unsigned long long)pool.n_slots) {
+            const float4 d = __ldg(&pool.ray_d[mine]);
+            if (__float_as_int(d.w) == 1) {
+              const float4 o = __ldg(&pool.ray_o[mine]);
+              slot = (int)mine;
+              r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
+              aux = make_aux(r, sc.filter_ok);
+              i = 0; tCur = INF; prim = -1;
+            }
+          }
+        }
+      }
+    }
+    // ---- walk phase: box tests while enough lanes are walking
+    bool walking = slot >= 0 && i < n;
+    const unsigned mW = __ballot_sync(FULL, walking);
+    if (!mW) {
+      if (__ballot_sync(FULL, slot >= 0)) continue;    // only finished rays left: store them
+      if (pool_dry) break;
+      continue;                                         // fetched nothing but dead slots: fetch again
+    }
+    do {
+      if (walking) {
+        float4 lo, hi;
+        load_node<SMEM>(nodes, i, lo, hi);
+        const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
+        if (COUNT) ++cnt.nodes;
+        const bool hit = (w7 == NODE_NO_BOX) ? true : box_hit<COUNT>(lo, hi, r, aux, 0.001f, tCur, COUNT ? &cnt.exact : nullptr);
+        if (w7 == NODE_INNER) {
+          i = hit ? i + 1 : w6;
+        } else {
+          i = i + 1;
+          if (hit) { pend0 = w6; pend1 = w7; walking = false; }
+        }
+        if (i >= n) walking = false;
+      }
+    } while (__popc(__ballot_sync(FULL, walking)) >= th_walk);
+  }
+
+  if (COUNT) {
+    for (int o = 16; o > 0; o >>= 1) {
+      cnt.nodes += __shfl_down_sync(FULL, cnt.nodes, o);
+      cnt.leaves += __shfl_down_sync(FULL, cnt.leaves, o);
+      cnt.exact += __shfl_down_sync(FULL, cnt.exact, o);
+      cnt.sph_leaves += __shfl_down_sync(FULL, cnt.sph_leaves, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&counters[2], cnt.nodes); atomicAdd(&counters[3], cnt.leaves); atomicAdd(&counters[4], cnt.exact);
+      atomicAdd(&counters[6], cnt.sph_leaves);
+    }
+  }
+}
+
+// ---- SHADE + REGENERATE ----------------------------------------------------------------------------
+// One thread per slot.  The frame's paths are numbered 0 .. n_tiles*32*sample_count-1: path id ->
+// (sample offset, 8x4 tile, pixel of the tile), so that slots regenerated together get neighbouring pixels.
+// counters: [0] paths, [1] segments, [7] segments that ended on a triangle (COUNT only)
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_wf_shade(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
+                                                  unsigned long long* counters) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  const bool in_pool = k < pool.n_slots;
+  if (k == 0) cur->ray = 0;          // the next extend wave starts at slot 0 (no extend kernel is running now)
+  Counters cnt = {0, 0, 0, 0, 0};
+  int bounce = -1;
+  uint32_t pixel = 0, sample = 0;
+  V3 L = mk(0, 0, 0), thr = mk(1, 1, 1);
+  Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
+  bool wrote_ray = false;
+  if (in_pool) {
+    const float4 t4 = pool.thr[k];
+    bounce = __float_as_int(t4.w);
+    if (bounce >= 0) {
+      const float4 o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
+      const int2 h = pool.hit[k];
+      const uint2 id = pool.id[k];
+      pixel = id.x; sample = id.y;
+      r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
+      thr = mk(t4.x, t4.y, t4.z); L = mk(l4.x, l4.y, l4.z);
+      const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
+      if (done) {
+        float* px = accum + (size_t)pixel * 3;
+        atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);     // result unused -> red.global.add.f32
+        bounce = -1;
+      } else wrote_ray = true;
+    }
+  }
+  // regeneration: slots without a path take the next path ids of the frame (one atomic per warp)
+  const unsigned long long total = (unsigned long long)A.n_tiles * 32ull * (unsigned long long)A.sample_count;
+  const bool want = in_pool && bounce < 0;
+  const unsigned need = __ballot_sync(FULL, want);
+  bool new_path = false;
+  if (need) {
+    unsigned long long base = 0;
+    const int leader = __ffs(need) - 1;
+    if (lane == leader) base = atomicAdd(&cur->path, (unsigned long long)__popc(need));
+    base = __shfl_sync(FULL, base, leader);
+    if (want) {
+      const unsigned long long mine = base + __popc(need & ((1u << lane) - 1));
+      if (mine < total) {
+        const unsigned q = (unsigned)(mine % ((unsigned long long)A.n_tiles * 32ull));
+        const int s_off = (int)(mine / ((unsigned long long)A.n_tiles * 32ull));
+        const int tile = (int)(q >> 5), l = (int)(q & 31);
+        const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
+        if (x < A.W && y < A.H) {
+          pixel = (uint32_t)(y * A.W + x);
+          sample = (uint32_t)(A.sample_begin + s_off);
+          r = generate_ray(A, x, y, pixel, sample);
+          L = mk(0, 0, 0); thr = mk(1, 1, 1); bounce = 0;
+          new_path = wrote_ray = true;
+        }
+      }
+    }
+  }
+  if (in_pool) {
+    if (wrote_ray) {
+      pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+      pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+      pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
+      pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
+      if (new_path) pool.id[k] = make_uint2(pixel, sample);
+    } else {
+      pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
+      pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+    }
+  }
+  // statistics + liveness: one atomic each per warp
+  const unsigned mNew = __ballot_sync(FULL, new_path), mSeg = __ballot_sync(FULL, wrote_ray);
+  unsigned long long th = cnt.tri_hits;
+  if (COUNT) for (int o = 16; o > 0; o >>= 1) th += __shfl_down_sync(FULL, th, o);
+  if (lane == 0) {
+    if (mNew) atomicAdd(&counters[0], (unsigned long long)__popc(mNew));
+    if (mSeg) { atomicAdd(&counters[1], (unsigned long long)__popc(mSeg)); atomicAdd(&cur->alive, (unsigned long long)__popc(mSeg)); }
+    if (COUNT && th) atomicAdd(&counters[7], th);
+  }
+}
+
+// marks every slot empty (before the first shade pass of a frame)
+__global__ void k_wf_reset(WfPool pool) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= pool.n_slots) return;
+  pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+  pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
+}
+
+}  // namespace srt

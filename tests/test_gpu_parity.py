@@ -262,6 +262,42 @@ def test_variants_agree(name, device, dev_scenes, scenes):
     assert k1["sphere_leaf_tests"] == k3["sphere_leaf_tests"] and k1["triangle_hits"] == k3["triangle_hits"]
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_wavefront_agrees(name, device, dev_scenes, scenes):
+    """Variant 2 (extend / shade waves over a slot pool) traces the same paths as the megakernel - same Philox
+    keys, same traversal - and differs only in the order a pixel's samples are summed (red.global.add)."""
+    s = scenes[name]
+    W, H, spp = SMALL[name]
+    kw = dict(width=W, height=H, spp=spp, seed=11)
+    a, ra, sa = dev_scenes[name].render(s.render_params(variant=1, **kw))
+    b, rb, sb = dev_scenes[name].render(s.render_params(variant=2, **kw))
+    assert sa.paths == sb.paths and sa.segments == sb.segments
+    assert sb.launches >= 3
+    fin = np.isfinite(a).all(axis=2)
+    assert (np.isfinite(b).all(axis=2) == fin).all()
+    assert np.abs(a[fin] - b[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max())
+    assert (np.abs(ra.astype(int) - rb.astype(int)) <= 1).all()
+    device.set_counters(True)
+    try:
+        _, _, ca = dev_scenes[name].render(s.render_params(variant=1, **kw), want_rgba=False)
+        k1 = device.last_counters()
+        _, _, cb = dev_scenes[name].render(s.render_params(variant=2, **kw), want_rgba=False)
+        k2 = device.last_counters()
+    finally:
+        device.set_counters(False)
+    assert ca.node_visits == cb.node_visits and ca.leaf_tests == cb.leaf_tests
+    assert k1["sphere_leaf_tests"] == k2["sphere_leaf_tests"] and k1["triangle_hits"] == k2["triangle_hits"]
+    # a slot pool smaller than the frame (many waves) and a sample sub-range give the same frame
+    import os
+    os.environ["SRT_WF"] = "4096,256,12"
+    try:
+        c, _, sc_ = dev_scenes[name].render(s.render_params(variant=2, **kw), want_rgba=False)
+    finally:
+        del os.environ["SRT_WF"]
+    assert sc_.segments == sa.segments and sc_.launches > sb.launches
+    assert np.abs(a[fin] - c[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max())
+
+
 def test_full_size_properties(dev_scenes, scenes):
     """BASELINE config 4 geometry (1280x720) at reduced spp: every pixel written, counters consistent."""
     s = scenes["c3_masterchief"]
