@@ -257,8 +257,13 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   srt_scene* s = new srt_scene;
   s->dev = dev;
 #define SCK(expr) do { srt_status rc_ = (expr); if (rc_) { srt_scene_destroy(s); return rc_; } } while (0)
+  const int n_real = (int)nodes.size();
+  {  // sentinel at index n (not counted in n_nodes): a box-less leaf without primitives, see walk_step
+    Node t; t.lo = make_float4(0, 0, 0, 0); t.hi = make_float4(0, 0, i2f(-1), i2f(NODE_NO_BOX));
+    nodes.push_back(t);
+  }
   SCK(upload(s, nodes, &s->sc.nodes));
-  s->sc.n_nodes = (int)nodes.size();
+  s->sc.n_nodes = n_real;
   s->sc.filter_ok = filter_ok ? 1 : 0;
   s->node_bytes = nodes.size() * sizeof(Node);
   s->nodes_in_smem = s->node_bytes > 0 && s->node_bytes <= dev->smem_optin;

@@ -32,7 +32,7 @@ __device__ __forceinline__ void store_ray(srt_ray* q, const Ray& r) {
 __device__ __forceinline__ const Node* stage_nodes(const Scene& sc, bool in_smem, float4* smem) {
   if (!in_smem) return sc.nodes;
   const float4* src = reinterpret_cast<const float4*>(sc.nodes);
-  for (int k = threadIdx.x; k < sc.n_nodes * 2; k += blockDim.x) smem[k] = __ldg(&src[k]);
+  for (int k = threadIdx.x; k < (sc.n_nodes + 1) * 2; k += blockDim.x) smem[k] = __ldg(&src[k]);   // + the sentinel
   __syncthreads();
   return reinterpret_cast<const Node*>(smem);
 }

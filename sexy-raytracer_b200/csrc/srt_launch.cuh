@@ -55,7 +55,7 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   cudaError_t e;
   if (plan.variant == 2) {
     // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
-    plan.wf_slots = 1 << 21; plan.threads = 1024; plan.wf_th_walk = 20;
+    plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
     if (const char* t = getenv("SRT_WF")) {
       int a = 0, b = 0, c = 0;
       if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
@@ -146,13 +146,15 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   int th_walk = plan.wf_th_walk;
   void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
   void* extend_args[] = {&sc, &pool, &cur, &th_walk, &ctr};
-  const unsigned shade_blocks = (unsigned)((N + 255) / 256);
+  const unsigned reset_blocks = (unsigned)((N + 255) / 256);
+  unsigned shade_blocks = (unsigned)dev->sm_count * 6;            // persistent: 3 resident CTAs per SM, two rounds
+  if (shade_blocks > reset_blocks) shade_blocks = reset_blocks;
   int launches = 0;
 
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaMemsetAsync(cur, 0, sizeof(WfCursors), dev->stream));
   CK(cudaEventRecord(dev->ev0, dev->stream));
-  k_wf_reset<<<shade_blocks, 256, 0, dev->stream>>>(pool);
+  k_wf_reset<<<reset_blocks, 256, 0, dev->stream>>>(pool);
   ++launches;
   // The host learns (alive, path cursor) of wave j when it is about to launch wave j + LAG: the queue never drains,
   // and at most LAG empty waves run after the frame is finished.

@@ -32,6 +32,37 @@ struct WfPool {
 // [2] slots still alive after the last shade, [3] unused
 struct WfCursors { unsigned long long path, ray, alive, pad; };
 
+// One box test of the ordered traversal, written without data-dependent branches (the exact
+// re-evaluation of an undecided filtered test is the one rare exception): the ALU pipe (FMNMX, compares,
+// selects: one warp instruction per two cycles per scheduler) bounds this loop, so control is kept to selects.
+// The node array carries a SENTINEL at index n (NODE_NO_BOX leaf without primitives): every ray ends by
+// "hitting" it, which clears `walking` and leaves i = n + 1 - no separate end-of-array compare per step.
+template <bool COUNT, bool SMEM>
+__device__ __forceinline__ void walk_step(const Node* nodes, int n, const Ray& r, const RayAux& x, int& i, float tCur,
+                                          int& pend0, int& pend1, bool& walking, Counters& cnt) {
+  float4 lo, hi;
+  load_node<SMEM>(nodes, i, lo, hi);
+  const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
+  if (COUNT && i < n) ++cnt.nodes;
+  const float ax = fmaf(lo.x, x.idx, -x.oidx), bx = fmaf(lo.w, x.idx, -x.oidx);
+  const float ay = fmaf(lo.y, x.idy, -x.oidy), by = fmaf(hi.x, x.idy, -x.oidy);
+  const float az = fmaf(lo.z, x.idz, -x.oidz), bz = fmaf(hi.y, x.idz, -x.oidz);
+  const float l = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.001f));
+  const float h = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tCur));
+  const float slack = fmaf(9.5367432e-7f, x.M + fabsf(l) + fabsf(h), 1e-30f);   // x.M = +inf when the filter is off
+  const float diff = h - l;
+  bool hit = diff > 0.0f;
+  const bool nobox = w7 == NODE_NO_BOX;
+  if (!(fabsf(diff) > slack) && !nobox) {          // undecided (or NaN, or filter off): the reference's own arithmetic
+    if (COUNT) ++cnt.exact;
+    hit = box_hit_exact(lo, hi, r, 0.001f, tCur);
+  }
+  hit = hit || nobox;
+  const bool inner = w7 == NODE_INNER;
+  i = (inner && !hit) ? w6 : i + 1;
+  if (hit && !inner) { pend0 = w6; pend1 = w7; walking = false; }
+}
+
 // ---- EXTEND ------------------------------------------------------------------------------------------
 template <bool COUNT, bool SMEM, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
@@ -48,7 +79,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
   Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
   RayAux aux = make_aux(r, 0);
   int slot = -1;                   // -1: this lane holds no ray
-  int i = n, pend0 = -1, pend1 = -1, prim = -1;
+  int i = n + 1, pend0 = -1, pend1 = -1, prim = -1;
   float tCur = INF;
   bool pool_dry = false;           // warp-uniform: the wave's rays are all handed out
 
@@ -67,7 +98,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
       pend0 = pend1 = -1;
     }
     // ---- service phase 2: finished rays store their hit
-    if (slot >= 0 && i >= n && pend0 < 0) {
+    if (slot >= 0 && i > n) {
       pool.hit[slot] = make_int2(prim, __float_as_int(tCur));
       slot = -1;
     }
@@ -89,6 +120,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
               slot = (int)mine;
               r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
               aux = make_aux(r, sc.filter_ok);
+              if (!aux.ok) aux.M = INF;          // walk_step then always takes the exact test
               i = 0; tCur = INF; prim = -1;
             }
           }
@@ -96,7 +128,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
       }
     }
     // ---- walk phase: box tests while enough lanes are walking
-    bool walking = slot >= 0 && i < n;
+    bool walking = slot >= 0 && i <= n;
     const unsigned mW = __ballot_sync(FULL, walking);
     if (!mW) {
       if (__ballot_sync(FULL, slot >= 0)) continue;    // only finished rays left: store them
@@ -104,20 +136,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
       continue;                                         // fetched nothing but dead slots: fetch again
     }
     do {
-      if (walking) {
-        float4 lo, hi;
-        load_node<SMEM>(nodes, i, lo, hi);
-        const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
-        if (COUNT) ++cnt.nodes;
-        const bool hit = (w7 == NODE_NO_BOX) ? true : box_hit<COUNT>(lo, hi, r, aux, 0.001f, tCur, COUNT ? &cnt.exact : nullptr);
-        if (w7 == NODE_INNER) {
-          i = hit ? i + 1 : w6;
-        } else {
-          i = i + 1;
-          if (hit) { pend0 = w6; pend1 = w7; walking = false; }
-        }
-        if (i >= n) walking = false;
-      }
+#pragma unroll
+      for (int rep = 0; rep < 2; rep++)     // two steps per vote
+        if (walking) walk_step<COUNT, SMEM>(nodes, n, r, aux, i, tCur, pend0, pend1, walking, cnt);
     } while (__popc(__ballot_sync(FULL, walking)) >= th_walk);
   }
 
@@ -136,56 +157,71 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
 }
 
 // ---- SHADE + REGENERATE ----------------------------------------------------------------------------
-// One thread per slot.  The frame's paths are numbered 0 .. n_tiles*32*sample_count-1: path id ->
-// (sample offset, 8x4 tile, pixel of the tile), so that slots regenerated together get neighbouring pixels.
+// One thread per slot, persistent blocks striding over 256-slot chunks.  The frame's paths are numbered
+// 0 .. n_tiles*32*sample_count-1: path id -> (sample offset, 8x4 tile, pixel of the tile), so that slots
+// regenerated together get neighbouring pixels.  Path ids are allocated with ONE global atomic per chunk
+// (a per-warp atomic on the single cursor address serialised the whole kernel: profiles/r1_wavefront.md);
+// statistics stay in registers until the block ends.
 // counters: [0] paths, [1] segments, [7] segments that ended on a triangle (COUNT only)
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_wf_shade(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
                                                   unsigned long long* counters) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
+  __shared__ unsigned s_cnt[8];
+  __shared__ unsigned long long s_base;
+  __shared__ unsigned long long s_stat[3];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
-  const bool in_pool = k < pool.n_slots;
-  if (k == 0) cur->ray = 0;          // the next extend wave starts at slot 0 (no extend kernel is running now)
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur->ray = 0;    // the next extend wave starts at slot 0 (no extend kernel runs now)
+  if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+  const unsigned long long per_sample = (unsigned long long)A.n_tiles * 32ull;
+  const unsigned long long total = per_sample * (unsigned long long)A.sample_count;
   Counters cnt = {0, 0, 0, 0, 0};
-  int bounce = -1;
-  uint32_t pixel = 0, sample = 0;
-  V3 L = mk(0, 0, 0), thr = mk(1, 1, 1);
-  Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
-  bool wrote_ray = false;
-  if (in_pool) {
-    const float4 t4 = pool.thr[k];
-    bounce = __float_as_int(t4.w);
-    if (bounce >= 0) {
-      const float4 o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
+  unsigned n_new = 0, n_seg = 0;
+
+  for (int chunk = blockIdx.x; chunk * 256 < pool.n_slots; chunk += gridDim.x) {
+    const int k = chunk * 256 + threadIdx.x;
+    const bool in_pool = k < pool.n_slots;
+    int bounce = -1;
+    uint32_t pixel = 0, sample = 0;
+    V3 L = mk(0, 0, 0), thr = mk(1, 1, 1);
+    Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
+    bool wrote_ray = false;
+    if (in_pool) {
+      // all six loads are issued before the first use (a slot without a path reads stale but valid memory)
+      const float4 t4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
       const int2 h = pool.hit[k];
       const uint2 id = pool.id[k];
-      pixel = id.x; sample = id.y;
-      r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
-      thr = mk(t4.x, t4.y, t4.z); L = mk(l4.x, l4.y, l4.z);
-      const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
-      if (done) {
-        float* px = accum + (size_t)pixel * 3;
-        atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);     // result unused -> red.global.add.f32
-        bounce = -1;
-      } else wrote_ray = true;
+      bounce = __float_as_int(t4.w);
+      if (bounce >= 0) {
+        pixel = id.x; sample = id.y;
+        r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
+        thr = mk(t4.x, t4.y, t4.z); L = mk(l4.x, l4.y, l4.z);
+        const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
+        if (done) {
+          float* px = accum + (size_t)pixel * 3;
+          atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);     // result unused -> red.global.add.f32
+          bounce = -1;
+        } else wrote_ray = true;
+      }
     }
-  }
-  // regeneration: slots without a path take the next path ids of the frame (one atomic per warp)
-  const unsigned long long total = (unsigned long long)A.n_tiles * 32ull * (unsigned long long)A.sample_count;
-  const bool want = in_pool && bounce < 0;
-  const unsigned need = __ballot_sync(FULL, want);
-  bool new_path = false;
-  if (need) {
-    unsigned long long base = 0;
-    const int leader = __ffs(need) - 1;
-    if (lane == leader) base = atomicAdd(&cur->path, (unsigned long long)__popc(need));
-    base = __shfl_sync(FULL, base, leader);
+    // regeneration: slots without a path take the next path ids of the frame
+    const bool want = in_pool && bounce < 0;
+    const unsigned need = __ballot_sync(FULL, want);
+    if (lane == 0) s_cnt[warp] = __popc(need);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned run = 0;
+#pragma unroll
+      for (int w = 0; w < 8; w++) { const unsigned c = s_cnt[w]; s_cnt[w] = run; run += c; }
+      s_base = run ? atomicAdd(&cur->path, (unsigned long long)run) : total;
+    }
+    __syncthreads();
+    bool new_path = false;
     if (want) {
-      const unsigned long long mine = base + __popc(need & ((1u << lane) - 1));
+      const unsigned long long mine = s_base + s_cnt[warp] + __popc(need & ((1u << lane) - 1));
       if (mine < total) {
-        const unsigned q = (unsigned)(mine % ((unsigned long long)A.n_tiles * 32ull));
-        const int s_off = (int)(mine / ((unsigned long long)A.n_tiles * 32ull));
+        const unsigned q = (unsigned)(mine % per_sample);
+        const int s_off = (int)(mine / per_sample);
         const int tile = (int)(q >> 5), l = (int)(q & 31);
         const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
         if (x < A.W && y < A.H) {
@@ -197,27 +233,34 @@ __global__ void __launch_bounds__(256) k_wf_shade(Scene sc, RenderArgs A, WfPool
         }
       }
     }
-  }
-  if (in_pool) {
-    if (wrote_ray) {
-      pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-      pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
-      pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
-      pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
-      if (new_path) pool.id[k] = make_uint2(pixel, sample);
-    } else {
-      pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
-      pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+    if (in_pool) {
+      if (wrote_ray) {
+        pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+        pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+        pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
+        pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
+        if (new_path) pool.id[k] = make_uint2(pixel, sample);
+      } else {                                    // no path: extend skips the slot, the next shade pass retries
+        pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
+        pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+      }
     }
+    n_new += new_path ? 1u : 0u;
+    n_seg += wrote_ray ? 1u : 0u;
+    __syncthreads();                              // s_cnt / s_base are reused by the next chunk
   }
-  // statistics + liveness: one atomic each per warp
-  const unsigned mNew = __ballot_sync(FULL, new_path), mSeg = __ballot_sync(FULL, wrote_ray);
-  unsigned long long th = cnt.tri_hits;
-  if (COUNT) for (int o = 16; o > 0; o >>= 1) th += __shfl_down_sync(FULL, th, o);
-  if (lane == 0) {
-    if (mNew) atomicAdd(&counters[0], (unsigned long long)__popc(mNew));
-    if (mSeg) { atomicAdd(&counters[1], (unsigned long long)__popc(mSeg)); atomicAdd(&cur->alive, (unsigned long long)__popc(mSeg)); }
-    if (COUNT && th) atomicAdd(&counters[7], th);
+  // statistics + liveness: one atomic per counter per block
+  unsigned long long v0 = n_new, v1 = n_seg, v2 = cnt.tri_hits;
+  for (int o = 16; o > 0; o >>= 1) {
+    v0 += __shfl_down_sync(FULL, v0, o); v1 += __shfl_down_sync(FULL, v1, o);
+    if (COUNT) v2 += __shfl_down_sync(FULL, v2, o);
+  }
+  if (lane == 0) { atomicAdd(&s_stat[0], v0); atomicAdd(&s_stat[1], v1); if (COUNT) atomicAdd(&s_stat[2], v2); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
+    if (s_stat[1]) { atomicAdd(&counters[1], s_stat[1]); cur->alive = 1; }     // flag, not a count
+    if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
   }
 }
 
