@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(Scene sc, int nodes_in_smem,
       h.uv[0] = h.uv[1] = 0;
     } else {
       Rec rec;
-      finish_hit(sc, prim, r, t, true, true, rec);
+      finish_hit<false>(sc, prim, r, t, true, true, rec);
       h.prim = rec.prim; h.mat = rec.mat; h.front_face = rec.front_face; h.t = rec.t;
       h.p[0] = rec.p.x; h.p[1] = rec.p.y; h.p[2] = rec.p.z;
       h.normal[0] = rec.normal.x; h.normal[1] = rec.normal.y; h.normal[2] = rec.normal.z;
@@ -109,7 +109,7 @@ __device__ __forceinline__ bool shade_segment(const Scene& sc, const RenderArgs&
                                      : __float_as_int(__ldg(&sc.sphs[prim - sc.n_tri].c.y));
   const Mat m = sc.mats[mat_id];
   Rec rec;
-  finish_hit(sc, prim, r, t, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
+  finish_hit<true>(sc, prim, r, t, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
   const uint4 x4 = philox(A.seed, pixel, sample, 2u + (uint32_t)bounce);
   V3 rvec = mk(0, 0, 0);
   if (m.kind == SRT_MAT_PBR) rvec = sample_unit_vector(u01(x4.x), u01(x4.y));
@@ -117,7 +117,7 @@ __device__ __forceinline__ bool shade_segment(const Scene& sc, const RenderArgs&
   V3 e = material_emitted(sc, m, rec);
   L = mk(L.x + thr.x * e.x, L.y + thr.y * e.y, L.z + thr.z * e.z);
   V3 att; Ray next;
-  if (!material_scatter(sc, m, r, rec, rvec, u01(x4.z), att, next)) return true;
+  if (!material_scatter<true>(sc, m, r, rec, rvec, u01(x4.z), att, next)) return true;
   thr = mk(thr.x * att.x, thr.y * att.y, thr.z * att.z);
   if (A.rr_begin > 0 && bounce + 1 >= A.rr_begin) {     // Russian roulette: not in the reference, off by default
     float q = fminf(fmaxf(fmaxf(thr.x, fmaxf(thr.y, thr.z)), 0.05f), 1.0f);
@@ -232,7 +232,7 @@ __global__ void k_shade_kat(Scene sc, const srt_ray* __restrict__ rays, const sr
   const Mat m = sc.mats[rec.mat];
   V3 e = material_emitted(sc, m, rec), a = mk(0, 0, 0);
   Ray o; o.o = o.d = mk(0, 0, 0); o.time = 0;
-  bool ok = material_scatter(sc, m, r, rec, mk(xi[4 * i], xi[4 * i + 1], xi[4 * i + 2]), xi[4 * i + 3], a, o);
+  bool ok = material_scatter<false>(sc, m, r, rec, mk(xi[4 * i], xi[4 * i + 1], xi[4 * i + 2]), xi[4 * i + 3], a, o);
   if (!ok && m.kind == SRT_MAT_LIGHT) { o.o = o.d = mk(0, 0, 0); o.time = 0; }
   att[3 * i] = a.x; att[3 * i + 1] = a.y; att[3 * i + 2] = a.z;
   emit[3 * i] = e.x; emit[3 * i + 1] = e.y; emit[3 * i + 2] = e.z;

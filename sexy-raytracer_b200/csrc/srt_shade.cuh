@@ -13,6 +13,18 @@ struct Rec {
   int front_face, mat, prim;
 };
 
+// unitVector (vec3.h:54-60).  FAST = the render kernels: one MUFU.RSQ and three products instead of three IEEE
+// divisions (<= 2 ulp from the reference's value; shading needs statistical parity only, and the 1e-5 bar on
+// normals holds a fortiori).  The known-answer entry points (srt_trace_rays, srt_shade_kat) use the exact form.
+template <bool FAST>
+__device__ __forceinline__ V3 unit_v(V3 v) {
+  if (!FAST) return unit_vector(v);
+  const float l2 = length_squared(v);
+  if (l2 == 0.0f) return v;
+  const float inv = rsqrtf(l2);
+  return mk(v.x * inv, v.y * inv, v.z * inv);
+}
+
 // hittable.h:18-21
 __device__ __forceinline__ void set_face_normal(Rec& rec, const Ray& r, V3 outward) {
   rec.front_face = dot(r.d, outward) < 0;
@@ -22,13 +34,14 @@ __device__ __forceinline__ void set_face_normal(Rec& rec, const Ray& r, V3 outwa
 // The part of triangle::hit after the accept (model.h:156-178) + calcTangentBasis (model.h:214-235).
 // Deferred to the one primitive whose record survives the traversal: every field is a function of
 // (primitive, ray, t) only.
+template <bool FAST>
 __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ray& r, float t, bool want_uv, bool want_tbn,
                                                 Rec& rec) {
   const float4 A = __ldg(&sc.tris[i].a), B = __ldg(&sc.tris[i].b), C = __ldg(&sc.tris[i].c), D = __ldg(&sc.tris[i].d);
   V3 v0 = mk(A.x, A.y, A.z), v1 = mk(B.x, B.y, B.z), v2 = mk(C.x, C.y, C.z), N = mk(A.w, B.w, C.w);
   rec.t = t;
   rec.p = mk(r.o.x + t * r.d.x, r.o.y + t * r.d.y, r.o.z + t * r.d.z);     // ray.at(t), ray.h:15-17
-  set_face_normal(rec, r, unit_vector(N));
+  set_face_normal(rec, r, unit_v<FAST>(N));
   rec.mat = __float_as_int(D.y);
   rec.prim = i;
   rec.u = rec.v = 0.0f;
@@ -49,9 +62,9 @@ __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ra
       float f = (du0x * du1y - du1x * du0y);
       if (f == 0) f += FLT_EPSILON;
       f = 1.0f / f;
-      rec.tangent = unit_vector(mk(f * (du1y * e0.x - du0y * e1.x), f * (du1y * e0.y - du0y * e1.y),
+      rec.tangent = unit_v<FAST>(mk(f * (du1y * e0.x - du0y * e1.x), f * (du1y * e0.y - du0y * e1.y),
                                    f * (du1y * e0.z - du0y * e1.z)));
-      rec.bitangent = unit_vector(mk(f * (-du1x * e0.x + du0x * e1.x), f * (-du1x * e0.y + du0x * e1.y),
+      rec.bitangent = unit_v<FAST>(mk(f * (-du1x * e0.x + du0x * e1.x), f * (-du1x * e0.y + du0x * e1.y),
                                      f * (-du1x * e0.z + du0x * e1.z)));
     }
   }
@@ -59,13 +72,14 @@ __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ra
 
 // The part of sphere::hit after the root is chosen (sphere.h:74-81), getSphereUV (:32-38),
 // calcTangentBasis (:96-106)
+template <bool FAST>
 __device__ __forceinline__ void finish_sphere(const Scene& sc, int j, const Ray& r, float t, bool want_uv, bool want_tbn,
                                               Rec& rec) {
   const float4 a = __ldg(&sc.sphs[j].a), b = __ldg(&sc.sphs[j].b), c = __ldg(&sc.sphs[j].c);
   V3 ctr = sph_center(a, b, c, r.time);
   rec.t = t;
   rec.p = mk(r.o.x + t * r.d.x, r.o.y + t * r.d.y, r.o.z + t * r.d.z);
-  V3 outward = unit_vector(rec.p - ctr);
+  V3 outward = unit_v<FAST>(rec.p - ctr);
   set_face_normal(rec, r, outward);
   rec.mat = __float_as_int(c.y);
   rec.prim = sc.n_tri + j;
@@ -82,15 +96,16 @@ __device__ __forceinline__ void finish_sphere(const Scene& sc, int j, const Ray&
     float ndoty = outward.x * 0.0f + (outward.y * 1.0f + outward.z * 0.0f);
     if (1.0f - fabsf(ndoty) < FLT_EPSILON) bb = mk(-0.0f, -0.0f, -1.0f);
     else bb = mk(0.0f, 1.0f, 0.0f);
-    rec.tangent = unit_vector(cross(bb, outward));
-    rec.bitangent = unit_vector(cross(outward, rec.tangent));
+    rec.tangent = unit_v<FAST>(cross(bb, outward));
+    rec.bitangent = unit_v<FAST>(cross(outward, rec.tangent));
   }
 }
 
+template <bool FAST>
 __device__ __forceinline__ void finish_hit(const Scene& sc, int prim, const Ray& r, float t, bool want_uv, bool want_tbn,
                                            Rec& rec) {
-  if (prim < sc.n_tri) finish_triangle(sc, prim, r, t, want_uv, want_tbn, rec);
-  else finish_sphere(sc, prim - sc.n_tri, r, t, want_uv, want_tbn, rec);
+  if (prim < sc.n_tri) finish_triangle<FAST>(sc, prim, r, t, want_uv, want_tbn, rec);
+  else finish_sphere<FAST>(sc, prim - sc.n_tri, r, t, want_uv, want_tbn, rec);
 }
 
 // ---- texture::value -----------------------------------------------------------------------------
@@ -144,13 +159,14 @@ __device__ __forceinline__ V3 material_emitted(const Scene& sc, const Mat& m, co
 }
 
 // material::scatter.  rvec: unit vector (PBR) / point in the unit ball (METAL); xi: DIELECTRIC's draw.
+template <bool FAST>
 __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, const Ray& rIn, const Rec& rec, V3 rvec,
                                                  float xi, V3& attenuation, Ray& out) {
   if (m.kind == SRT_MAT_LIGHT) return false;                              // material.h:144-146
   out.o = rec.p;
   out.time = rIn.time;
   if (m.kind == SRT_MAT_METAL) {                                          // material.h:91-97
-    V3 reflected = reflect(unit_vector(rIn.d), rec.normal);
+    V3 reflected = reflect(unit_v<FAST>(rIn.d), rec.normal);
     out.d = mk(reflected.x + m.fuzz * rvec.x, reflected.y + m.fuzz * rvec.y, reflected.z + m.fuzz * rvec.z);
     attenuation = mk(m.albedo[0], m.albedo[1], m.albedo[2]);
     return dot(out.d, rec.normal) > 0;
@@ -158,7 +174,7 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
   if (m.kind == SRT_MAT_DIELECTRIC) {                                     // material.h:108-126,132-136
     attenuation = mk(1.0f, 1.0f, 1.0f);
     float ratio = rec.front_face ? (1.0f / m.ir) : m.ir;
-    V3 unitDir = unit_vector(rIn.d);
+    V3 unitDir = unit_v<FAST>(rIn.d);
     float cosTheta = fminf(dot(rec.normal, -unitDir), 1.0f);
     float sinTheta = sqrtf(1.0f - cosTheta * cosTheta);
     bool cannotRefract = ratio * sinTheta > 1.0f;
@@ -180,7 +196,7 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
     V3 n = texture_value(sc, m.normal_tex, rec.u, rec.v, rec.p);
     n = mk((n.x - 128.0f) / 128.0f, (n.y - 128.0f) / 128.0f, (n.z - 128.0f) / 128.0f);     // vec3.h:103-110
     const V3 T = rec.tangent, B = rec.bitangent, N = rec.normal;
-    normal = unit_vector(mk(T.x * n.x + (B.x * n.y + N.x * n.z), T.y * n.x + (B.y * n.y + N.y * n.z),
+    normal = unit_v<FAST>(mk(T.x * n.x + (B.x * n.y + N.x * n.z), T.y * n.x + (B.y * n.y + N.y * n.z),
                             T.z * n.x + (B.z * n.y + N.z * n.z)));
   } else normal = rec.normal;
   if (m.metallic_tex >= 0) mm = clampf(texture_value(sc, m.metallic_tex, rec.u, rec.v, rec.p).x / 255.0f, 0, 1.0f);
@@ -191,10 +207,10 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
   V3 sd = normal + rvec;
   // vec3.h:49-52 compares fabs() < 1e-8 in double; (double)x < 1e-8  <=>  x <= fl32(1e-8)
   if (fabsf(sd.x) <= 1e-8f && fabsf(sd.y) <= 1e-8f && fabsf(sd.z) <= 1e-8f) sd = normal;
-  sd = unit_vector(sd);
+  sd = unit_v<FAST>(sd);
   out.d = sd;
-  V3 viewVec = -unit_vector(rIn.d);
-  V3 halfVec = unit_vector(sd + viewVec);
+  V3 viewVec = -unit_v<FAST>(rIn.d);
+  V3 halfVec = unit_v<FAST>(sd + viewVec);
   float NdotL = fmaxf(dot(normal, sd), 0.0f);
   float NdotH = fmaxf(dot(normal, halfVec), 0.0f);
   float HdotV = fmaxf(dot(halfVec, viewVec), 0.0f);
@@ -241,13 +257,13 @@ __device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0
 // sampled directly instead of by rejection (no data-dependent loop inside a warp)
 __device__ __forceinline__ void sample_disk(float xa, float xb, float& dx, float& dy) {
   float r = sqrtf(xa), phi = (2.0f * SRT_PI) * xb, s, c;
-  sincosf(phi, &s, &c);
+  __sincosf(phi, &s, &c);         // phi in [0, 2 pi): absolute error 2^-21, no range-reduction slow path
   dx = r * c; dy = r * s;
 }
 __device__ __forceinline__ V3 sample_unit_vector(float xa, float xb) {
   float z = 1.0f - 2.0f * xa;
   float rxy = sqrtf(fmaxf(0.0f, 1.0f - z * z)), phi = (2.0f * SRT_PI) * xb, s, c;
-  sincosf(phi, &s, &c);
+  __sincosf(phi, &s, &c);
   return mk(rxy * c, rxy * s, z);
 }
 __device__ __forceinline__ V3 sample_unit_ball(float xa, float xb, float xc) {

@@ -33,15 +33,43 @@ struct WfPool {
 struct WfCursors { unsigned long long path, ray, alive, pad; };
 
 // One box test of the ordered traversal, written without data-dependent branches (the exact
-// re-evaluation of an undecided filtered test is the one rare exception): the ALU pipe (FMNMX, compares,
-// selects: one warp instruction per two cycles per scheduler) bounds this loop, so control is kept to selects.
+// re-evaluation of an undecided filtered test is the one rare exception): the loop is issue bound, so
+// control is a handful of predicate operations and two selects.
 // The node array carries a SENTINEL at index n (NODE_NO_BOX leaf without primitives): every ray ends by
-// "hitting" it, which clears `walking` and leaves i = n + 1 - no separate end-of-array compare per step.
+// "hitting" it - no end-of-array compare per step.  A lane that hits a leaf's box stops walking with i
+// still on that leaf; the service phase reads its primitives from the node again.
+// Lane state is ONE integer: i >= 0 = walking, next node i;  i < 0 = stopped on node ~i.
+// `nodes_s` is the 32-bit shared-window address of the staged tree (SMEM) - LDS needs no generic->shared
+// conversion per step that way.
+//
+// Shared-memory layout (SMEM): the two 16-byte halves of the nodes are staged as two arrays lo[n+1], hi[n+1]
+// instead of 32-byte records.  The loop is bound by shared-memory wavefronts (every lane reads a different
+// node): with 32-byte records all `lo` halves fall into 4 of the 8 bank groups, so the 8 lanes of a quarter
+// warp collide ~3.4 deep; with 16-byte stride they spread over all 8 (~2.4 deep).
+template <bool SMEM>
+__device__ __forceinline__ void load_node_soa(const Node* nodes, uint32_t nodes_s, uint32_t hi_off, int i, float4& lo, float4& hi) {
+  if (SMEM) {
+    const uint32_t a = nodes_s + (uint32_t)i * 16u;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w) : "r"(a));
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "r"(a + hi_off));
+  } else {
+    lo = __ldg(&nodes[i].lo); hi = __ldg(&nodes[i].hi);
+  }
+}
+
+// cooperative staging of the (n + 1)-node array as lo[] | hi[]
+__device__ __forceinline__ void stage_nodes_soa(const Scene& sc, float4* smem) {
+  const float4* src = reinterpret_cast<const float4*>(sc.nodes);
+  const int n1 = sc.n_nodes + 1;
+  for (int k = threadIdx.x; k < n1 * 2; k += blockDim.x) smem[(k & 1) * n1 + (k >> 1)] = __ldg(&src[k]);
+  __syncthreads();
+}
+
 template <bool COUNT, bool SMEM>
-__device__ __forceinline__ void walk_step(const Node* nodes, int n, const Ray& r, const RayAux& x, int& i, float tCur,
-                                          int& pend0, int& pend1, bool& walking, Counters& cnt) {
+__device__ __forceinline__ void walk_step(const Node* nodes, uint32_t nodes_s, uint32_t hi_off, int n, const Ray& r, const RayAux& x,
+                                          int& i, float tCur, Counters& cnt) {
   float4 lo, hi;
-  load_node<SMEM>(nodes, i, lo, hi);
+  load_node_soa<SMEM>(nodes, nodes_s, hi_off, i, lo, hi);
   const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
   if (COUNT && i < n) ++cnt.nodes;
   const float ax = fmaf(lo.x, x.idx, -x.oidx), bx = fmaf(lo.w, x.idx, -x.oidx);
@@ -59,8 +87,8 @@ __device__ __forceinline__ void walk_step(const Node* nodes, int n, const Ray& r
   }
   hit = hit || nobox;
   const bool inner = w7 == NODE_INNER;
-  i = (inner && !hit) ? w6 : i + 1;
-  if (hit && !inner) { pend0 = w6; pend1 = w7; walking = false; }
+  const int next = (inner && !hit) ? w6 : i + 1;
+  i = (hit && !inner) ? ~i : next;
 }
 
 // ---- EXTEND ------------------------------------------------------------------------------------------
@@ -68,41 +96,48 @@ template <bool COUNT, bool SMEM, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
                                                           unsigned long long* counters) {
   extern __shared__ float4 smem_nodes[];
-  const Node* nodes = stage_nodes(sc, SMEM, smem_nodes);
+  const Node* nodes = sc.nodes;
+  if (SMEM) stage_nodes_soa(sc, smem_nodes);
   const int lane = threadIdx.x & 31;
   const unsigned FULL = 0xffffffffu;
   const int n = sc.n_nodes;
+  const uint32_t hi_off = (uint32_t)(n + 1) * 16u;
   const float INF = __int_as_float(0x7f800000);
   Counters cnt = {0, 0, 0, 0, 0};
-  if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // counted anew by the next shade pass
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // set anew by the next shade pass
 
   Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
   RayAux aux = make_aux(r, 0);
+  const uint32_t nodes_s = SMEM ? (uint32_t)__cvta_generic_to_shared(smem_nodes) : 0u;
   int slot = -1;                   // -1: this lane holds no ray
-  int i = n + 1, pend0 = -1, pend1 = -1, prim = -1;
+  int i = -1, prim = -1;           // i >= 0: walking, next node i;  i < 0 with a slot: stopped on node ~i (hit leaf, or sentinel = done)
   float tCur = INF;
   bool pool_dry = false;           // warp-uniform: the wave's rays are all handed out
 
   for (;;) {
-    // ---- service phase 1: leaf tests of pending primitives, in reference order
-    if (pend0 >= 0) {
+    // ---- service phase 1: lanes stopped on a leaf test its primitives in reference order; on the sentinel, store the hit
+    if (slot >= 0 && i < 0) {
+      const int at = ~i;
+      if (at >= n) {
+        pool.hit[slot] = make_int2(prim, __float_as_int(tCur));
+        slot = -1;
+      } else {
+        float4 lo, hi;
+        load_node_soa<SMEM>(nodes, nodes_s, hi_off, at, lo, hi);
+        const int pa = __float_as_int(hi.z), pb = __float_as_int(hi.w);
 #pragma unroll 1
-      for (int k = 0; k < 2; k++) {
-        const int p = k == 0 ? pend0 : pend1;
-        if (p < 0) break;
-        if (COUNT) { ++cnt.leaves; if (p >= sc.n_tri) ++cnt.sph_leaves; }
-        float t;
-        const bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
-        if (acc) { tCur = t; prim = p; }
+        for (int k = 0; k < 2; k++) {
+          const int p = k == 0 ? pa : pb;
+          if (p < 0) break;
+          if (COUNT) { ++cnt.leaves; if (p >= sc.n_tri) ++cnt.sph_leaves; }
+          float t;
+          const bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
+          if (acc) { tCur = t; prim = p; }
+        }
+        i = at + 1;
       }
-      pend0 = pend1 = -1;
     }
-    // ---- service phase 2: finished rays store their hit
-    if (slot >= 0 && i > n) {
-      pool.hit[slot] = make_int2(prim, __float_as_int(tCur));
-      slot = -1;
-    }
-    // ---- service phase 3: idle lanes fetch the next rays of the wave (one atomic per warp)
+    // ---- service phase 2: idle lanes fetch the next rays of the wave (one atomic per warp)
     if (!pool_dry) {
       const unsigned need = __ballot_sync(FULL, slot < 0);
       if (need) {
@@ -114,9 +149,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
         if (slot < 0) {
           const unsigned long long mine = base + __popc(need & ((1u << lane) - 1));
           if (mine < (unsigned long long)pool.n_slots) {
-            const float4 d = __ldg(&pool.ray_d[mine]);
+            const float4 d = __ldg(&pool.ray_d[mine]), o = __ldg(&pool.ray_o[mine]);   // both in flight together
             if (__float_as_int(d.w) == 1) {
-              const float4 o = __ldg(&pool.ray_o[mine]);
               slot = (int)mine;
               r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
               aux = make_aux(r, sc.filter_ok);
@@ -128,18 +162,17 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
       }
     }
     // ---- walk phase: box tests while enough lanes are walking
-    bool walking = slot >= 0 && i <= n;
-    const unsigned mW = __ballot_sync(FULL, walking);
+    const unsigned mW = __ballot_sync(FULL, i >= 0);
     if (!mW) {
-      if (__ballot_sync(FULL, slot >= 0)) continue;    // only finished rays left: store them
+      if (__ballot_sync(FULL, slot >= 0)) continue;    // only stopped lanes left: serve them
       if (pool_dry) break;
       continue;                                         // fetched nothing but dead slots: fetch again
     }
     do {
 #pragma unroll
       for (int rep = 0; rep < 2; rep++)     // two steps per vote
-        if (walking) walk_step<COUNT, SMEM>(nodes, n, r, aux, i, tCur, pend0, pend1, walking, cnt);
-    } while (__popc(__ballot_sync(FULL, walking)) >= th_walk);
+        if (i >= 0) walk_step<COUNT, SMEM>(nodes, nodes_s, hi_off, n, r, aux, i, tCur, cnt);
+    } while (__popc(__ballot_sync(FULL, i >= 0)) >= th_walk);
   }
 
   if (COUNT) {
