@@ -179,7 +179,8 @@ def run_b200(args):
     dev.set_stream(stream.cuda_stream)          # library launches + torch events + NCCL on ONE stream
     ds = dev.upload(scene)
     begin, count = sample_split(spp, world, rank)
-    P = scene.render_params(width=W, height=H, spp=spp, max_bounce=depth, sample_begin=begin, sample_count=count, seed=2026)
+    P = scene.render_params(width=W, height=H, spp=spp, max_bounce=depth, sample_begin=begin, sample_count=count, seed=2026,
+                            variant=args.variant)
     accum = torch.zeros(H * W * 3, dtype=torch.float32, device="cuda")
     rgba = torch.zeros(H * W * 4, dtype=torch.uint8, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")    # > 126 MB L2
@@ -204,8 +205,9 @@ def run_b200(args):
     if rank == 0:
         clocks.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    seg = paths = 0
-    kern_ms = 0.0
+    seg = paths = launches = ext_launches = 0
+    kern_ms = ext_ms = shd_ms = 0.0
+    variant = 0
     barrier()
     for a, b in ev:
         flush.fill_(1)                           # L2 flush between timed iterations, outside the event pair
@@ -216,6 +218,9 @@ def run_b200(args):
         b.record(stream)
         if st is not None:
             seg += int(st.segments); paths += int(st.paths); kern_ms += st.kernel_ms
+            ext_ms += st.extend_ms; shd_ms += st.shade_ms; ext_launches += st.extend_launches
+            launches += st.launches; variant = st.variant
+        launches += 1 if rank == 0 else 0                          # k_resolve
     barrier()
     ms = sum(a.elapsed_time(b) for a, b in ev)
     clk = clocks.stop() if rank == 0 else None
@@ -264,32 +269,43 @@ def run_b200(args):
         # ---- roofline of the dominant kernel (k_render_mega): counters from a short counted pass of the same frame
         dev.set_counters(True)
         stc = ds.render_accumulate(accum.data_ptr(), scene.render_params(width=W, height=H, spp=spp, max_bounce=depth,
-                                                                         sample_begin=0, sample_count=max(1, min(8, spp)), seed=2026))
+                                                                         sample_begin=0, sample_count=max(1, min(8, spp)), seed=2026,
+                                                                         variant=variant))
         c = dev.last_counters()
         dev.set_counters(False)
-        bps, k = algorithmic_bytes_per_segment(c, int(stc.segments))
+        bps_all, k = algorithmic_bytes_per_segment(c, int(stc.segments))
+        # the traversal kernel's part of SURVEY 8(d)'s figure: node + primitive fetches + the ray; the accept-time UV and
+        # texel bytes belong to the shade kernel
+        bps = 32 * k["B"] + 36 * k["Lt"] + 40 * k["Ls"] + 28
+        kname = {1: "k_render_mega", 2: "k_wf_extend", 3: "k_render_phased"}.get(variant, "?")
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
-        seg_rank0 = seg / max(1, args.steps)                   # rank 0's segments per launch
-        launch_s = kern_ms / max(1, args.steps) * 1e-3
+        n_l = max(1, ext_launches)
+        seg_rank0 = seg / n_l                                  # rank 0's segments (= rays traced) per launch of the dominant kernel
+        launch_s = ext_ms / n_l * 1e-3                         # its average launch duration, CUDA events inside the timed region
         achieved = bps * seg_rank0 / launch_s / 1e9
-        fl = flops_per_segment(k) * seg_rank0 / launch_s / 1e12
+        fl_seg = 27 * k["B"] + 65 * k["Lt"] + 25 * k["Ls"]     # traversal kernel's part of SURVEY 8(d)'s flop figure
+        fl = fl_seg * seg_rank0 / launch_s / 1e12
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
         fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
-        roofline = {"kernel": "k_render_mega", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak_hbm,
+        roofline = {"kernel": kname, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak_hbm,
                     "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "unit": "GB/s",
                     "frac": round(achieved / peak_hbm, 4), "traffic": None,
-                    "bytes_per_segment": round(bps, 1), "per_segment": {a: round(b, 3) for a, b in k.items()},
-                    "segments_per_launch": seg_rank0, "launch_ms": round(launch_s * 1e3, 3),
-                    "note": "algorithmic bytes are node/primitive fetches; for this scene they are served from shared memory "
-                            "and L1/L2 (whole BVH staged per CTA), so DRAM traffic is far below them - see profiles/",
+                    "bytes_per_segment": round(bps, 1), "bytes_per_segment_whole_path": round(bps_all, 1),
+                    "per_segment": {a: round(b, 3) for a, b in k.items()},
+                    "segments_per_launch": round(seg_rank0, 1), "launch_ms": round(launch_s * 1e3, 4),
+                    "launches_per_step": round(n_l / max(1, args.steps), 1),
+                    "share_of_step": {kname: round(ext_ms / max(kern_ms, 1e-9), 4), "k_wf_shade": round(shd_ms / max(kern_ms, 1e-9), 4)},
+                    "note": "algorithmic bytes are node/primitive/ray fetches of the traversal kernel; for this scene the nodes are served "
+                            "from shared memory (whole BVH staged per CTA) and primitives from L1/L2, so DRAM traffic is far below "
+                            "them and frac may exceed what HBM alone could deliver - see profiles/ and DESIGN.md 'Rooflines'",
                     "fp32": {"achieved_tflops": round(fl, 3), "peak_nominal_tflops": round(fp32_peak, 1),
                              "frac_fma_peak": round(fl / fp32_peak, 4), "frac_unfused_peak": round(fl / (fp32_peak / 2), 4),
-                             "flops_per_segment": round(flops_per_segment(k), 1)}}
+                             "flops_per_segment": round(fl_seg, 1)}}
         cpu = None
         if world == 1 and not args.no_cpu:
             v, desc = cpu_frame_sample(args)
@@ -308,7 +324,7 @@ def run_b200(args):
                         "s_per_step": round(te.item() / args.steps, 4),
                         "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out)" if world == 1 else
                                 "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H"},
-                "gpu_launches": args.steps * 2, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}
+                "gpu_launches": launches, "variant": variant, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}
     ds.close()
     dev.close()
     if world > 1:
@@ -351,6 +367,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the samples per pixel of the config (not the headline)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 flat megakernel, 2 wavefront, 3 phased megakernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

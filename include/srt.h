@@ -166,7 +166,8 @@ typedef struct srt_render_params {
   float    background[3];  /* main.cpp:170                                                       */
   uint64_t seed;           /* Philox key                                                         */
   int32_t  rr_begin;       /* Russian roulette from this bounce on; 0 = off (the reference has none) */
-  int32_t  variant;        /* 0 = auto, 1 = megakernel, 2 = wavefront                            */
+  int32_t  variant;        /* 0 = auto (wavefront for frames of >= 4 Mi paths over trees of >= 256 nodes, else megakernel),
+                              1 = flat megakernel, 2 = wavefront, 3 = phased megakernel         */
 } srt_render_params;
 
 typedef struct srt_stats {
@@ -176,6 +177,12 @@ typedef struct srt_stats {
   uint64_t leaf_tests;     /* triangle::hit + sphere::hit calls (only when counters are enabled) */
   float    kernel_ms;      /* device time of the render kernel(s), CUDA events on the launch stream */
   int32_t  launches;       /* kernels launched by the call                                       */
+  /* per-kernel device time (CUDA events on the launch stream around each launch):
+     traversal = k_wf_extend launches (wavefront) or the whole megakernel; shade = k_wf_shade      */
+  float    extend_ms;
+  float    shade_ms;
+  int32_t  extend_launches;
+  int32_t  variant;        /* the variant that ran: 1 flat megakernel, 2 wavefront, 3 phased megakernel */
 } srt_stats;
 
 typedef struct srt_device srt_device;

@@ -41,8 +41,10 @@ struct srt_device {
   WfCursors* d_wf_cur = nullptr;
   WfCursors* h_wf_ring = nullptr;             // pinned, WF_RING entries
   cudaEvent_t wf_ev[8] = {};
+  cudaEvent_t wf_t[16][3] = {};               // per-wave timing ring: before shade, after shade, after extend
 };
 static const int WF_RING = 8;
+static const int WF_TRING = 16;
 
 struct srt_scene {
   srt_device* dev = nullptr;
@@ -100,6 +102,7 @@ void srt_device_destroy(srt_device* d) {
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
   for (int k = 0; k < WF_RING; k++) if (d->wf_ev[k]) cudaEventDestroy(d->wf_ev[k]);
+  for (int k = 0; k < WF_TRING; k++) for (int q = 0; q < 3; q++) if (d->wf_t[k][q]) cudaEventDestroy(d->wf_t[k][q]);
   if (d->ev0) cudaEventDestroy(d->ev0);
   if (d->ev1) cudaEventDestroy(d->ev1);
   if (d->own_stream) cudaStreamDestroy(d->own_stream);

@@ -48,7 +48,10 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   srt_device* dev = s->dev;
   plan.threads = 512;
   plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
-  plan.variant = P->variant ? P->variant : 3;
+  // auto: the wavefront needs a few waves over a large slot pool to amortise its launches; small frames stay in one megakernel
+  // (measured, B200: C3/C4 1.7x faster as waves; C1 equal; C2's 11-node tree 2x faster in the megakernel)
+  plan.variant = P->variant ? P->variant
+                            : (((long long)A.n_tiles * 32 * A.sample_count >= (4ll << 20) && s->sc.n_nodes >= 256) ? 2 : 1);
   plan.tune = PhaseTune{16, 12, 20};
   plan.fn = nullptr;
   int per_sm = 0;
@@ -129,6 +132,7 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     CK(cudaMalloc(&dev->d_wf_cur, sizeof(WfCursors)));
     CK(cudaMallocHost(&dev->h_wf_ring, WF_RING * sizeof(WfCursors)));
     for (int k = 0; k < WF_RING; k++) CK(cudaEventCreateWithFlags(&dev->wf_ev[k], cudaEventDisableTiming));
+    for (int k = 0; k < WF_TRING; k++) for (int q = 0; q < 3; q++) CK(cudaEventCreate(&dev->wf_t[k][q]));
   }
   WfPool pool = dev->wf;
   {  // carve the SoA arrays out of the one allocation (capacity-strided so the layout survives smaller frames)
@@ -159,18 +163,33 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   // The host learns (alive, path cursor) of wave j when it is about to launch wave j + LAG: the queue never drains,
   // and at most LAG empty waves run after the frame is finished.
   const int LAG = 4;
+  double shade_ms = 0, extend_ms = 0;
+  long long waves = 0, timed = 0;
+  auto collect = [&](long long w) -> cudaError_t {      // wave w is known to be complete
+    cudaEvent_t* t = dev->wf_t[w % WF_TRING];
+    float a = 0, b = 0;
+    cudaError_t e = cudaEventElapsedTime(&a, t[0], t[1]);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&b, t[1], t[2]);
+    shade_ms += a; extend_ms += b; ++timed;
+    return e;
+  };
   for (long long j = 0;; j++) {
     if (j >= LAG) {
       const int slot = (int)((j - LAG) % WF_RING);
-      CK(cudaEventSynchronize(dev->wf_ev[slot]));
+      CK(cudaEventSynchronize(dev->wf_ev[slot]));       // after wave j-LAG's shade => wave j-LAG-1 is complete
+      if (j >= LAG + 1) CK(collect(j - LAG - 1));
       const WfCursors& c = dev->h_wf_ring[slot];
       if (c.alive == 0 && c.path >= total) break;
     }
+    cudaEvent_t* t = dev->wf_t[j % WF_TRING];
+    CK(cudaEventRecord(t[0], dev->stream));
     CK(cudaLaunchKernel(plan.wf_shade, dim3(shade_blocks), dim3(256), shade_args, 0, dev->stream));
+    CK(cudaEventRecord(t[1], dev->stream));
     CK(cudaMemcpyAsync(&dev->h_wf_ring[j % WF_RING], cur, sizeof(WfCursors), cudaMemcpyDeviceToHost, dev->stream));
     CK(cudaEventRecord(dev->wf_ev[j % WF_RING], dev->stream));
     CK(cudaLaunchKernel(plan.fn, dim3(plan.blocks), dim3(plan.threads), extend_args, plan.smem, dev->stream));
-    launches += 2;
+    CK(cudaEventRecord(t[2], dev->stream));
+    launches += 2; ++waves;
   }
   CK(cudaEventRecord(dev->ev1, dev->stream));
   unsigned long long h[8];
@@ -181,6 +200,9 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     stats->paths = h[0]; stats->segments = h[1]; stats->node_visits = h[2]; stats->leaf_tests = h[3];
     float ms = 0; CK(cudaEventElapsedTime(&ms, dev->ev0, dev->ev1));
     stats->kernel_ms = ms; stats->launches = launches;
+    for (long long w = timed; w < waves; w++) CK(collect(w));     // the last LAG+1 waves (the stream is idle now)
+    stats->extend_ms = (float)extend_ms; stats->shade_ms = (float)shade_ms;
+    stats->extend_launches = (int)waves; stats->variant = 2;
   }
   return SRT_OK;
 }
@@ -208,6 +230,7 @@ srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, sr
     stats->paths = h[0]; stats->segments = h[1]; stats->node_visits = h[2]; stats->leaf_tests = h[3];
     float ms = 0; CK(cudaEventElapsedTime(&ms, dev->ev0, dev->ev1));
     stats->kernel_ms = ms; stats->launches = 1;
+    stats->extend_ms = ms; stats->shade_ms = 0; stats->extend_launches = 1; stats->variant = plan.variant;
   }
   return SRT_OK;
 }
