@@ -1,0 +1,48 @@
+/* srt_host.h — C ABI of the HOST side helpers that sit immediately before the path ("libsrt_host.so", plain C++,
+ * no CUDA): the parts of scene construction whose results the device consumes and that must equal the
+ * reference's bit for bit.
+ *
+ *   srt_bvh_build    : bvhNode::bvhNode(objects, 0, n, time0, time1)   (reference bvh.h:55-95), in place
+ *   srt_camera_make  : camera::camera(...)                              (reference camera.h:10-38)
+ *   srt_prim_boxes   : triangle::boundingBox / sphere::boundingBox      (reference model.h:183-212, sphere.h:85-94)
+ *
+ * Why a builder of our own: the reference constructor copies the whole object vector at EVERY node (bvh.h:57), i.e.
+ * O(N^2) - 92 ms for 3 046 primitives, unusable for BASELINE config 5 (10.1 M primitives); and triangle holds uint16
+ * indices (model.h:46).  This builder sorts each node's span in place (children only ever look at their own slice, so
+ * the result is identical), draws the split axes from the same std::mt19937 stream in the same pre-order, uses the same
+ * comparator (box minimum at time 0, bvh.h:32-40) with the same std::sort, and builds sub-trees on several threads
+ * (the tree SHAPE depends on n alone, so every node's pre-order index - hence its random draw - is known up front).
+ */
+#ifndef SRT_HOST_H_
+#define SRT_HOST_H_
+
+#include "srt.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Boxes of the primitives of `prims` (nodes / tables ignored): out[i*6..] = min.xyz, max.xyz over [time0, time1],
+ * primitive order = triangles then spheres.                                                                  */
+srt_status srt_prim_boxes(const srt_scene_desc* prims, float time0, float time1, float* out_boxes);
+
+/* Builds the tree over all primitives of `prims`.
+ *  rng_skip   : outputs of the default-seeded std::mt19937 (seed 5489) already consumed by randomFloat() before the
+ *               bvhNode constructor runs (0 for main.cpp's default scene; each randomFloat() = one output)
+ *  threads    : worker threads (<= 0: hardware concurrency)
+ *  out_nodes  : malloc'ed array in srt_bvh_node form (pre-order, root 0), free with srt_bvh_free
+ *  out_draws  : optional, number of random outputs the build consumed (= number of nodes)                      */
+srt_status srt_bvh_build(const srt_scene_desc* prims, float time0, float time1, uint64_t rng_skip, int threads,
+                         srt_bvh_node** out_nodes, int64_t* out_n_nodes, uint64_t* out_draws);
+void       srt_bvh_free(srt_bvh_node* nodes);
+
+/* camera.h:10-38: the ten derived members from (eye, lookAt, up, vFOV degrees, aspect, aperture, focusDist, t0, t1) */
+srt_status srt_camera_make(const float eye[3], const float look_at[3], const float up[3], float vfov, float aspect,
+                           float aperture, float focus_dist, float time0, float time1, srt_camera* out);
+
+const char* srt_host_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRT_HOST_H_ */

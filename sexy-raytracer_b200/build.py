@@ -30,6 +30,20 @@ def build_cuda(force=False, verbose=False):
     return LIB
 
 
+HOST_LIB = os.path.join(HERE, "libsrt_host.so")
+
+
+def build_host(force=False):
+    """libsrt_host.so: the host-side helpers of include/srt_host.h (BVH builder, camera constructor); plain g++."""
+    src = os.path.join(HERE, "host", "srt_host.cpp")
+    deps = [src, os.path.join(ROOT, "include", "srt_host.h"), os.path.join(ROOT, "include", "srt.h")]
+    if not force and not _stale(HOST_LIB, deps):
+        return HOST_LIB
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-Wall",
+                           "-I" + os.path.join(ROOT, "include"), src, "-o", HOST_LIB, "-lpthread"])
+    return HOST_LIB
+
+
 def build_oracles():
     """The checkers: plain-C oracle always; the compiled reference only where /root/reference exists."""
     subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "all"])
