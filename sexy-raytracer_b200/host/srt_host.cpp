@@ -216,13 +216,15 @@ srt_status srt_camera_make(const float eye[3], const float look_at[3], const flo
   if (!eye || !look_at || !up || !c) return fail(SRT_ERR_INVALID, "NULL argument");
   const float pi = 3.1415926535897932385f;                      // globals.h:15
   const float theta = vfov * pi / 180.0f;                       // deg2rad, globals.h:26-28
-  const float h = tanf(theta / 2.0f);                           // <cmath> float overload of tan
-  const float vp_h = 2.0f * h, vp_w = aspect * vp_h;
+  // `auto h = tan(theta / 2.0f)` (camera.h:20) resolves to ::tan(double): h, vpHeight and vpWidth are doubles, and
+  // `focusDist * vpWidth * hor` rounds the double product to float once (Eigen converts the scalar factor to float)
+  const double h = tan((double)(theta / 2.0f));
+  const double vp_h = 2.0f * h, vp_w = aspect * vp_h;
   float d[3] = {eye[0] - look_at[0], eye[1] - look_at[1], eye[2] - look_at[2]}, t[3];
   unit3(d, c->w);
   cross3(up, c->w, t); unit3(t, c->hor);
   cross3(c->w, c->hor, t); unit3(t, c->vert);
-  const float sw = focus_dist * vp_w, sh = focus_dist * vp_h;
+  const float sw = (float)(focus_dist * vp_w), sh = (float)(focus_dist * vp_h);
   for (int k = 0; k < 3; k++) {
     c->origin[k] = eye[k];
     c->horizontal[k] = sw * c->hor[k];
