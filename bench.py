@@ -37,12 +37,14 @@ CONFIGS = {  # name -> (scene file, W, H, spp, max_bounce)
     "c2": ("c2_cube", 640, 360, 64, 8),
     "c3": ("c3_masterchief", 426, 240, 1000, 4),
     "c4": ("c3_masterchief", 1280, 720, 5000, 4),
+    "c5": (None, 1920, 1080, 256, 16),          # synthetic: built on the fly (sexy_raytracer_b200.synth)
 }
 WORKLOAD_NAMES = {
     "c1": "Shirley sphere scene 400x225 16spp depth 10 (BASELINE config 1)",
     "c2": "cube.gltf+square.gltf 640x360 64spp depth 8 (BASELINE config 2)",
     "c3": "main.cpp default scene (Master Chief + globe) 426x240 1000spp depth 4 (BASELINE config 3)",
     "c4": "main.cpp default scene (Master Chief + globe) 1280x720 5000spp depth 4, spp split across GPUs (BASELINE config 4)",
+    "c5": "synthetic stress: 10M-triangle random mesh + 100k spheres 1920x1080 256spp depth 16 (BASELINE config 5)",
 }
 
 
@@ -51,6 +53,12 @@ def load_workload(args):
     name, W, H, spp, depth = CONFIGS[args.config]
     if args.spp:
         spp = args.spp
+    if name is None:
+        from sexy_raytracer_b200.synth import make_stress_scene
+        t = time.perf_counter()
+        s = make_stress_scene(args.tris, args.spheres, width=W, height=H, spp=spp, depth=depth)
+        print("[bench] built %s: %d nodes in %.1f s" % (s.name, len(s.nodes), time.perf_counter() - t), file=sys.stderr, flush=True)
+        return s, W, H, spp, depth
     s = Scene.load(os.path.join(ROOT, "scenes", name + ".npz"))
     s.render = np.array([W, H, spp, depth], np.int32)
     return s, W, H, spp, depth
@@ -119,9 +127,31 @@ def _cpu_band(job):
     return int(st.segments), time.perf_counter() - t
 
 
-def cpu_frame_sample(args, seconds_per_core=12.0):
+def cpu_port_sample(args, scene, seconds_per_core=12.0):
+    """Config 5 (one 1.2 GB scene): the C port with one thread per core on a centred band of rows at 1 spp."""
+    from oracle import refbind
+    name, W, H, spp, depth = CONFIGS[args.config]
+    cores = os.cpu_count() or 1
+    rows = int(max(4, min(H, round(cores * 0.12e6 * seconds_per_core / 3.0 / W))))
+    y0 = (H - rows) // 2
+    P = refbind.PortOracle()
+    h = P.from_scene(scene)
+    t = time.perf_counter()
+    _, st = P.render(h, scene, scene.render_params(width=W, height=H, spp=1, max_bounce=depth, seed=1000), y0=y0, y1=y0 + rows,
+                     nthreads=cores)
+    dt = time.perf_counter() - t
+    P.free(h)
+    seg = int(st.segments)
+    return seg / dt / 1e6, {"kind": "port", "cores": cores, "unit": METRIC,
+                            "sample": "%dx%d frame, rows %d..%d, 1 spp (of %d), %d threads of one process; %.2f M segments in %.1f s"
+                            % (W, H, y0, y0 + rows, spp, cores, seg / 1e6, dt), "wall_s": round(dt, 2)}
+
+
+def cpu_frame_sample(args, seconds_per_core=12.0, scene=None):
     """A bounded sample of the workload on all host cores: every core renders its own band of rows of the same
     frame at a reduced spp.  -> (M segments/s, description dict)"""
+    if CONFIGS[args.config][0] is None:
+        return cpu_port_sample(args, scene, seconds_per_core)
     from oracle import refbind
     kind = "reference" if refbind.RefOracle.available() else "port"
     name, W, H, spp, depth = CONFIGS[args.config]
@@ -273,7 +303,7 @@ def run_b200(args):
                                                                          variant=variant))
         c = dev.last_counters()
         dev.set_counters(False)
-        bps_all, k = algorithmic_bytes_per_segment(c, int(stc.segments))
+        bps_all, k = algorithmic_bytes_per_segment(c, int(stc.segments), n_maps=0 if args.config == "c5" else 2)
         # the traversal kernel's part of SURVEY 8(d)'s figure: node + primitive fetches + the ray; the accept-time UV and
         # texel bytes belong to the shade kernel
         bps = 32 * k["B"] + 36 * k["Lt"] + 40 * k["Ls"] + 28
@@ -308,14 +338,17 @@ def run_b200(args):
                              "flops_per_segment": round(fl_seg, 1)}}
         cpu = None
         if world == 1 and not args.no_cpu:
-            v, desc = cpu_frame_sample(args)
+            v, desc = cpu_frame_sample(args, scene=scene)
             cpu = dict(value=round(v, 4), **desc)
         line = {"metric": METRIC, "value": round(value, 2), "unit": "M segments/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": round(ms_all / args.steps, 3), "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD_NAMES[args.config] + (" [spp overridden: %d]" % spp if args.spp else ""),
+                "config": {"workload": WORKLOAD_NAMES[args.config] + (" [spp overridden: %d]" % spp if args.spp else "")
+                           + (" [size overridden: %d triangles, %d spheres]" % (args.tris, args.spheres)
+                              if args.config == "c5" and (args.tris, args.spheres) != (10_000_000, 100_000) else ""),
                            "width": W, "height": H, "spp": spp, "max_bounce": depth, "parallelism": "spp-split x%d" % world,
-                           "scene": "committed flattening of the reference scene as it loads (globe maps missing upstream -> fallback colour)",
+                           "scene": ("synthetic, seeded; tree from the bvh.h-equivalent builder" if args.config == "c5" else
+                                     "committed flattening of the reference scene as it loads (globe maps missing upstream -> fallback colour)"),
                            "l2": "256 MiB flush write between timed steps"},
                 "frame_time_s": round(ms_all / args.steps / 1e3, 4), "spp_per_s": round(spp / (ms_all / args.steps / 1e3), 1),
                 "segments_per_step": seg_all / args.steps, "paths_per_step": paths_all / args.steps,
@@ -339,10 +372,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    _, W, H, spp, depth = load_workload(args)
+    scene, W, H, spp, depth = load_workload(args)
     vals, desc = [], None
     for i in range(args.warmup + args.steps):
-        v, desc = cpu_frame_sample(args, seconds_per_core=5.0)
+        v, desc = cpu_frame_sample(args, seconds_per_core=5.0, scene=scene)
         if i >= args.warmup:
             vals.append(v)
     value = sum(vals) / len(vals)
@@ -351,7 +384,8 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(desc["wall_s"] * 1e3, 1), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_NAMES[args.config], "width": W, "height": H, "spp": spp, "max_bounce": depth,
-                       "parallelism": "%d host processes on disjoint row bands (the reference is single threaded)" % cores},
+                       "parallelism": ("%d host threads of the C port on one band of rows" % cores if desc["kind"] == "port" else
+                                       "%d host processes on disjoint row bands (the reference is single threaded)" % cores)},
             "cpu_baseline": dict(value=round(value, 4), **desc),
             "e2e": {"value": round(value, 4), "unit": "M segments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -367,6 +401,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the samples per pixel of the config (not the headline)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--tris", type=int, default=10_000_000, help="config c5: triangles")
+    ap.add_argument("--spheres", type=int, default=100_000, help="config c5: spheres")
     ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 flat megakernel, 2 wavefront, 3 phased megakernel")
     args = ap.parse_args()
     if args.impl == "reference":
