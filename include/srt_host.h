@@ -35,10 +35,39 @@ srt_status srt_prim_boxes(const srt_scene_desc* prims, float time0, float time1,
 srt_status srt_bvh_build(const srt_scene_desc* prims, float time0, float time1, uint64_t rng_skip, int threads,
                          srt_bvh_node** out_nodes, int64_t* out_n_nodes, uint64_t* out_draws);
 void       srt_bvh_free(srt_bvh_node* nodes);
+/* As srt_bvh_build, for scenes whose objects were NOT inserted triangles-first: order[i] = primitive id (in the
+ * triangles-then-spheres numbering of srt.h) of the i-th object of the reference's `objects` vector.  std::sort is not
+ * stable, so the initial order of the vector is part of the contract.  order == NULL means identity.            */
+srt_status srt_bvh_build_ordered(const srt_scene_desc* prims, const int32_t* order, float time0, float time1, uint64_t rng_skip,
+                                 int threads, srt_bvh_node** out_nodes, int64_t* out_n_nodes, uint64_t* out_draws);
 
 /* camera.h:10-38: the ten derived members from (eye, lookAt, up, vFOV degrees, aspect, aperture, focusDist, t0, t1) */
 srt_status srt_camera_make(const float eye[3], const float look_at[3], const float up[3], float vfov, float aspect,
                            float aperture, float focus_dist, float time0, float time1, srt_camera* out);
+
+/* ---- images: stbi_load as imagePNG uses it (texture.h:112-123) and stbi_write_png (main.cpp:235-237) ---------------
+ * read : 8-bit samples converted to req_comp (1..4) channels by stb_image's rules, row 0 = top; *out_pixels is malloc'ed
+ *        with 4 spare zero bytes at the end, free with srt_host_free.
+ * write: 8-bit, comp = 1..4 channels, stride_bytes between rows (0 = w*comp).                                       */
+srt_status srt_png_read(const char* path, int32_t req_comp, int32_t* out_w, int32_t* out_h, uint8_t** out_pixels);
+srt_status srt_png_read_memory(const uint8_t* file_bytes, int64_t len, int32_t req_comp, int32_t* out_w, int32_t* out_h,
+                               uint8_t** out_pixels);
+srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, const uint8_t* pixels, int32_t stride_bytes);
+void       srt_host_free(void* p);
+
+/* ---- whole scenes through the C++ host classes of srt_world.hpp (for callers that are not C++: tests, bench) ----------
+ * which: 1 = the Shirley sphere block of main.cpp:92-122 re-enabled (+ main.cpp:124-131,143-144)   [BASELINE config 1]
+ *        2 = cube.gltf + square.gltf + ground + light                                              [BASELINE config 2]
+ *        3 = randomScene()'s default branch, main.cpp:72-76,82-90,126-146                          [BASELINE configs 3, 4]
+ *        4 = as 3, the globe's four maps pointed at files that exist in this checkout
+ * data_dir holds the reference's assets (its data/ directory).  The process-wide generator is reset first, as at the
+ * start of main().  The scene owns everything srt_host_scene_desc points at.                                      */
+typedef struct srt_host_scene srt_host_scene;
+srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_scene** out);
+srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int reference_quirks, srt_host_scene** out);
+const srt_scene_desc* srt_host_scene_desc(const srt_host_scene* s);
+uint64_t   srt_host_scene_draws(const srt_host_scene* s);      /* generator outputs consumed by the set-up */
+void       srt_host_scene_free(srt_host_scene* s);
 
 const char* srt_host_last_error(void);
 

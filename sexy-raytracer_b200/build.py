@@ -35,13 +35,28 @@ HOST_LIB = os.path.join(HERE, "libsrt_host.so")
 
 def build_host(force=False):
     """libsrt_host.so: the host-side helpers of include/srt_host.h (BVH builder, camera constructor); plain g++."""
-    src = os.path.join(HERE, "host", "srt_host.cpp")
-    deps = [src, os.path.join(ROOT, "include", "srt_host.h"), os.path.join(ROOT, "include", "srt.h")]
+    hdir = os.path.join(HERE, "host")
+    srcs = [os.path.join(hdir, f) for f in ("srt_host.cpp", "srt_png.cpp", "srt_world.cpp", "srt_scenes.cpp")]
+    deps = srcs + [os.path.join(hdir, "srt_json.hpp")] + [os.path.join(ROOT, "include", f) for f in ("srt_host.h", "srt.h", "srt_world.hpp")]
     if not force and not _stale(HOST_LIB, deps):
         return HOST_LIB
     subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-Wall",
-                           "-I" + os.path.join(ROOT, "include"), src, "-o", HOST_LIB, "-lpthread"])
+                           "-I" + os.path.join(ROOT, "include")] + srcs + ["-o", HOST_LIB, "-lpthread", "-lz", "-ldl"])
     return HOST_LIB
+
+
+EXAMPLE = os.path.join(ROOT, "examples", "sexy-raytracer")
+
+
+def build_example(force=False):
+    """examples/main.cpp: the reference's main.cpp over the host classes + the device (links libsrt_host.so only;
+    libsrt_b200.so is dlopen'ed at run time)."""
+    src = os.path.join(ROOT, "examples", "main.cpp")
+    if not force and not _stale(EXAMPLE, [src, HOST_LIB, os.path.join(ROOT, "include", "srt_world.hpp")]):
+        return EXAMPLE
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "include"), src, "-L" + HERE, "-lsrt_host",
+                           "-Wl,-rpath," + HERE, "-o", EXAMPLE])
+    return EXAMPLE
 
 
 def build_oracles():

@@ -16,10 +16,14 @@
 
 #include "../../include/srt_host.h"
 
-namespace {
-
+namespace srt_host_detail {
 thread_local std::string g_err;
 srt_status fail(srt_status s, const std::string& m) { g_err = m; return s; }
+}  // namespace srt_host_detail
+using srt_host_detail::fail;
+using srt_host_detail::g_err;
+
+namespace {
 
 struct Box { float mn[3], mx[3]; };
 
@@ -160,6 +164,11 @@ void srt_bvh_free(srt_bvh_node* nodes) { free(nodes); }
 
 srt_status srt_bvh_build(const srt_scene_desc* d, float time0, float time1, uint64_t rng_skip, int threads,
                          srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) {
+  return srt_bvh_build_ordered(d, nullptr, time0, time1, rng_skip, threads, out_nodes, out_n, out_draws);
+}
+
+srt_status srt_bvh_build_ordered(const srt_scene_desc* d, const int32_t* order, float time0, float time1, uint64_t rng_skip,
+                                 int threads, srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) {
   if (!d || !out_nodes || !out_n) return fail(SRT_ERR_INVALID, "NULL argument");
   *out_nodes = nullptr; *out_n = 0;
   if (d->n_tri < 0 || d->n_sph < 0) return fail(SRT_ERR_INVALID, "negative count");
@@ -183,10 +192,17 @@ srt_status srt_bvh_build(const srt_scene_desc* d, float time0, float time1, uint
           B.pbox[p] = prim_box(d, p, time0, time1);
           const Box b0 = prim_box(d, p, 0.0f, 0.0f);             // boxCompare: boundingBox(0, 0, ...), bvh.h:36
           for (int k = 0; k < 3; k++) B.key[k][p] = b0.mn[k];
-          B.ids[p] = (int32_t)p;
+          B.ids[p] = order ? order[p] : (int32_t)p;
         }
       });
     for (auto& t : pool) t.join();
+  }
+  if (order) {                                                     // must be a permutation of [0, n)
+    std::vector<uint8_t> seen((size_t)n, 0);
+    for (int64_t p = 0; p < n; p++) {
+      if (order[p] < 0 || order[p] >= n || seen[order[p]]) return fail(SRT_ERR_INVALID, "order is not a permutation of the primitive ids");
+      seen[order[p]] = 1;
+    }
   }
   // one randomInt(0, 2) per node, drawn in construction (= pre-order) order from the reference's generator:
   // static std::uniform_real_distribution<float>(0, 1) over a default-seeded std::mt19937 (globals.h:30-43)

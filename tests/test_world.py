@@ -1,0 +1,289 @@
+"""The host side of the drop-in (include/srt_world.hpp -> libsrt_host.so): the scene classes with the reference's
+constructor signatures, the glTF reader, the PNG codec, the flattening.  CPU tests; the last one drives the example
+main.cpp-equivalent on the GPU."""
+import base64
+import ctypes as C
+import io
+import json
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, SCENES
+from sexy_raytracer_b200 import abi, host
+from sexy_raytracer_b200.scene import Scene
+
+REF_DATA = "/root/reference/data"
+needs_ref_data = pytest.mark.skipif(not os.path.isdir(REF_DATA), reason="the reference's data/ directory is not on this box")
+
+
+def _same(a, b):
+    return a.shape == b.shape and a.tobytes() == b.tobytes()
+
+
+# ---- the four reference scenes, built by the C++ host classes, equal the compiled reference's own export -------------
+@needs_ref_data
+@pytest.mark.parametrize("which,name", [(1, "c1_shirley"), (2, "c2_cube"), (3, "c3_masterchief"), (4, "c3s_globe")])
+def test_host_classes_reproduce_reference_flattening(which, name, scenes):
+    """scenes/*.npz were exported by the compiled reference (oracle/make_golden.py -> ref_scene_export).  The same scene
+    written against srt_world.hpp (host/srt_scenes.cpp mirrors main.cpp:82-146 statement for statement) must flatten to
+    the identical bytes: geometry read by the glTF reader, texel bytes decoded by the PNG reader, the random sphere
+    parameters of main.cpp:92-122 (same generator, same draw order), material / texture tables, and the tree."""
+    s, draws = host.reference_scene(which, REF_DATA)
+    g = scenes[name]
+    for k in Scene.ARRAYS:
+        assert _same(getattr(s, k), getattr(g, k)), k
+    assert set(s.tex_data) == set(g.tex_data)
+    for i in g.tex_data:
+        assert np.array_equal(s.tex_data[i].ravel(), np.asarray(g.tex_data[i]).ravel()), "texel bytes of texture %d" % i
+    # one draw per node for the tree + the draws of the scene block (main.cpp:92-122 for config 1)
+    assert draws >= len(g.nodes)
+    if which != 1:
+        assert draws == len(g.nodes)
+
+
+def test_reference_scene_errors_are_loud(tmp_path):
+    with pytest.raises(RuntimeError):
+        host.reference_scene(3, str(tmp_path))          # no glTF there
+    with pytest.raises(RuntimeError):
+        host.reference_scene(9, str(tmp_path))
+    s, draws = host.reference_scene(1, str(tmp_path))   # config 1 needs no files
+    assert s.n_sph == 485 and s.n_tri == 0 and len(s.nodes) == 511
+
+
+# ---- PNG ---------------------------------------------------------------------------------------------------------------
+def _pil():
+    return pytest.importorskip("PIL.Image")
+
+
+def _stb(ref_so):
+    L = C.CDLL(ref_so)
+    L.stbi_load_from_memory.restype = C.POINTER(C.c_uint8)
+    L.stbi_load_from_memory.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
+    L.stbi_image_free.argtypes = [C.c_void_p]
+
+    def load(data, req):
+        w, h, n = C.c_int(), C.c_int(), C.c_int()
+        p = L.stbi_load_from_memory(data, len(data), C.byref(w), C.byref(h), C.byref(n), req)
+        assert p, "stb could not decode"
+        a = np.ctypeslib.as_array(p, shape=(h.value, w.value, req)).copy()
+        L.stbi_image_free(p)
+        return a
+    return load
+
+
+def _png_cases():
+    Image = _pil()
+    rng = np.random.default_rng(5)
+    out = {}
+    rgb = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    rgba = rng.integers(0, 256, (19, 31, 4), dtype=np.uint8)
+    grey = rng.integers(0, 256, (23, 29), dtype=np.uint8)
+    smooth = (np.add.outer(np.arange(64), np.arange(80)) * 2 % 256).astype(np.uint8)       # exercises every row filter
+    for name, im, kw in (("rgb", Image.fromarray(rgb, "RGB"), {}), ("rgba", Image.fromarray(rgba, "RGBA"), {}),
+                         ("grey", Image.fromarray(grey, "L"), {}), ("smooth", Image.fromarray(np.dstack([smooth] * 3), "RGB"), {"optimize": True}),
+                         ("la", Image.fromarray(np.dstack([grey, grey[::-1]]), "LA"), {}),
+                         ("pal", Image.fromarray(rgb, "RGB").quantize(16), {}), ("pal256", Image.fromarray(rgb, "RGB").quantize(200), {}),
+                         ("bw", Image.fromarray(grey > 127), {}),
+                         ("g16", Image.fromarray((grey.astype(np.uint16) * 257 + 13).astype(np.uint16)), {})):
+        b = io.BytesIO()
+        im.save(b, "PNG", **kw)
+        out[name] = b.getvalue()
+    return out
+
+
+def test_png_read_matches_pil():
+    Image = _pil()
+    for name, data in _png_cases().items():
+        im = Image.open(io.BytesIO(data))
+        if name in ("rgb", "smooth", "pal", "pal256"):
+            want = np.asarray(im.convert("RGB"))
+            assert np.array_equal(host.png_read(data, 3), want), name
+        if name in ("grey", "bw"):
+            want = np.asarray(im.convert("L"))
+            assert np.array_equal(host.png_read(data, 1)[:, :, 0], want), name
+            assert np.array_equal(host.png_read(data, 3), np.dstack([want] * 3)), name
+        if name == "rgba":
+            assert np.array_equal(host.png_read(data, 4), np.asarray(im)), name
+            assert np.array_equal(host.png_read(data, 3), np.asarray(im)[:, :, :3]), name
+
+
+def test_png_read_matches_stb(ref):
+    """Channel conversion and bit-depth rules are stb_image's (what imagePNG gets from stbi_load, texture.h:115): checked
+    against the stb_image compiled into the reference checker, for every colour type x requested channel count."""
+    from oracle import refbind
+    load = _stb(refbind.REF_SO)
+    for name, data in _png_cases().items():
+        for req in (1, 2, 3, 4):
+            assert np.array_equal(host.png_read(data, req), load(data, req)), (name, req)
+
+
+@needs_ref_data
+def test_png_read_reference_assets_vs_stb(ref):
+    from oracle import refbind
+    load = _stb(refbind.REF_SO)
+    for f, req in (("Image_0.png", 3), ("Image_1.png", 3), ("worldisyoursbanner.png", 1), ("rustediron2_metallic.png", 1),
+                   ("rustediron2_roughness.png", 3)):
+        data = open(os.path.join(REF_DATA, f), "rb").read()
+        assert np.array_equal(host.png_read(os.path.join(REF_DATA, f), req), load(data, req)), f
+
+
+def test_png_write_round_trip(tmp_path):
+    Image = _pil()
+    rng = np.random.default_rng(1)
+    for comp in (1, 2, 3, 4):
+        a = rng.integers(0, 256, (45, 61, comp), dtype=np.uint8)
+        p = str(tmp_path / ("w%d.png" % comp))
+        host.png_write(p, a)
+        assert np.array_equal(host.png_read(p, comp), a)
+        b = np.asarray(Image.open(p))                      # an independent decoder reads the file too
+        assert np.array_equal(b.reshape(a.shape), a)
+    with pytest.raises(RuntimeError):
+        host.png_read(str(tmp_path / "missing.png"), 3)
+    bad = tmp_path / "bad.png"
+    bad.write_bytes(b"\x89PNG\r\n\x1a\n" + b"junk" * 10)
+    with pytest.raises(RuntimeError):
+        host.png_read(str(bad), 3)
+
+
+# ---- glTF ----------------------------------------------------------------------------------------------------------------
+def _tiny_gltf(tmp_path, glb=False, idx_type=5123, acc_offset=0, translate=None, name="t"):
+    """Two triangles (a unit quad in z = 0) with UVs; optional accessor byteOffset, 32-bit indices, node translation."""
+    pos = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]], np.float32)
+    uv = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+    idx = np.array([0, 1, 2, 0, 2, 3], {5123: np.uint16, 5125: np.uint32, 5121: np.uint8}[idx_type])
+    pad = b"\xee" * acc_offset
+    blob = pad + pos.tobytes()
+    v0 = (0, len(blob))
+    o1 = len(blob); blob += uv.tobytes(); v1 = (o1, len(blob) - o1)
+    o2 = len(blob); blob += idx.tobytes(); v2 = (o2, len(blob) - o2)
+    blob += b"\0" * (-len(blob) % 4)
+    node = {"mesh": 0}
+    if translate is not None:
+        node["translation"] = list(translate)
+    doc = {"asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0]}], "nodes": [node],
+           "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [0.25, 0.5, 0.75, 1.0], "metallicFactor": 0.5,
+                                                   "roughnessFactor": 0.125}}],
+           "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "TEXCOORD_0": 1}, "indices": 2, "material": 0}]}],
+           "accessors": [{"bufferView": 0, "byteOffset": acc_offset, "componentType": 5126, "count": 4, "type": "VEC3"},
+                         {"bufferView": 1, "componentType": 5126, "count": 4, "type": "VEC2"},
+                         {"bufferView": 2, "componentType": idx_type, "count": 6, "type": "SCALAR"}],
+           "bufferViews": [{"buffer": 0, "byteOffset": v0[0], "byteLength": v0[1]}, {"buffer": 0, "byteOffset": v1[0], "byteLength": v1[1]},
+                           {"buffer": 0, "byteOffset": v2[0], "byteLength": v2[1]}],
+           "buffers": [{"byteLength": len(blob)}]}
+    if glb:
+        js = json.dumps(doc).encode()
+        js += b" " * (-len(js) % 4)
+        body = struct.pack("<II", len(js), 0x4E4F534A) + js + struct.pack("<II", len(blob), 0x004E4942) + blob
+        p = tmp_path / (name + ".glb")
+        p.write_bytes(b"glTF" + struct.pack("<II", 2, 12 + len(body)) + body)
+    else:
+        doc["buffers"][0]["uri"] = "data:application/octet-stream;base64," + base64.b64encode(blob).decode()
+        p = tmp_path / (name + ".gltf")
+        p.write_text(json.dumps(doc, indent=1))
+    return str(p), pos, uv
+
+
+@pytest.mark.parametrize("glb", [False, True])
+def test_gltf_reader_basic(tmp_path, glb):
+    path, pos, uv = _tiny_gltf(tmp_path, glb=glb)
+    s = host.gltf_scene(path)
+    assert s.n_tri == 2 and s.n_sph == 0 and len(s.nodes) == 1
+    assert np.array_equal(s.tri_v0, pos[[0, 0]]) and np.array_equal(s.tri_v1, pos[[1, 2]]) and np.array_equal(s.tri_v2, pos[[2, 3]])
+    assert np.array_equal(s.tri_uv1, uv[[1, 2]])
+    assert s.mat_kind.tolist() == [abi.SRT_MAT_PBR] and s.mat_tex.tolist() == [[-1, -1, -1, -1]]
+    assert np.allclose(s.mat_albedo[0], [0.25, 0.5, 0.75, 1.0]) and s.mat_params[0, 0] == 0.5 and s.mat_params[0, 1] == 0.125
+    assert sorted((~s.nodes["left"][0], ~s.nodes["right"][0])) == [0, 1]
+
+
+def test_gltf_reader_quirks_and_fixes(tmp_path):
+    """the reference reads from bufferView.byteOffset only, 16-bit indices only, no node transforms
+    (model.h:335-365,444-452).  referenceQuirks=True reproduces that; False honours accessor.byteOffset, the index
+    component type and node TRS."""
+    path, pos, _ = _tiny_gltf(tmp_path, acc_offset=12, idx_type=5125, translate=(10, 20, 30), name="q")
+    fixed = host.gltf_scene(path, reference_quirks=False)
+    assert fixed.n_tri == 2
+    assert np.array_equal(fixed.tri_v0, (pos + np.float32([10, 20, 30]))[[0, 0]])
+    assert np.array_equal(fixed.tri_v2, (pos + np.float32([10, 20, 30]))[[2, 3]])
+    quirky = host.gltf_scene(path, reference_quirks=True)
+    # 32-bit indices read as 16-bit: (0,0,1), (0,2,0) -> two degenerate triangles; positions start 12 bytes early
+    assert quirky.n_tri == 2 and not np.array_equal(quirky.tri_v0, fixed.tri_v0)
+    with pytest.raises(RuntimeError):
+        host.gltf_scene(str(tmp_path / "nope.gltf"))
+    bad = tmp_path / "bad.gltf"
+    bad.write_text("{ not json")
+    with pytest.raises(RuntimeError):
+        host.gltf_scene(str(bad))
+
+
+@needs_ref_data
+def test_gltf_reference_assets_both_modes():
+    """The reference's own assets carry no accessor offsets / strides / node transforms that matter, so both modes agree."""
+    for f in ("cube.gltf", "square.gltf", "masterchief2-separate-xf.gltf"):
+        a = host.gltf_scene(os.path.join(REF_DATA, f), REF_DATA + "/", True)
+        b = host.gltf_scene(os.path.join(REF_DATA, f), REF_DATA + "/", False)
+        for k in ("tri_v0", "tri_v1", "tri_v2", "tri_uv0", "tri_uv1", "tri_uv2", "tri_mat"):
+            assert _same(getattr(a, k), getattr(b, k)), (f, k)
+
+
+# ---- ordered builder -----------------------------------------------------------------------------------------------------
+def test_bvh_build_ordered(scenes):
+    s = scenes["c2_cube"]
+    L = host._bind_world(host.lib())
+    d = s.desc()
+    n = s.n_prim
+
+    def build(order):
+        out, cnt, draws = C.POINTER(abi.BvhNode)(), C.c_int64(), C.c_uint64()
+        o = None if order is None else np.ascontiguousarray(order, np.int32)
+        rc = L.srt_bvh_build_ordered(C.byref(d), None if o is None else o.ctypes.data_as(C.c_void_p), 0.0, 1.0, 0, 1,
+                                     C.byref(out), C.byref(cnt), C.byref(draws))
+        if rc != 0:
+            raise RuntimeError(L.srt_host_last_error().decode())
+        a = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_uint8)), shape=(cnt.value * 32,)).view(abi.NODE_DTYPE).copy()
+        L.srt_bvh_free(out)
+        return a
+
+    ident = build(np.arange(n))
+    assert _same(ident, build(None)) and _same(ident, s.nodes)
+    rev = build(np.arange(n)[::-1])
+    leaves = np.concatenate([~rev["left"][rev["left"] < 0], ~rev["right"][(rev["right"] < 0) & (rev["right"] != abi.SRT_BVH_NONE)]])
+    assert sorted(leaves.tolist()) == list(range(n))               # every primitive exactly once
+    assert _same(rev["bmin"][0], ident["bmin"][0]) and _same(rev["bmax"][0], ident["bmax"][0])
+    with pytest.raises(RuntimeError):
+        build(np.zeros(n))                                           # not a permutation
+
+
+# ---- the example program: the reference's main.cpp over the host classes + the device ---------------------------------
+def test_example_builds():
+    from sexy_raytracer_b200 import build
+    build.build_host()
+    exe = build.build_example()
+    assert os.access(exe, os.X_OK)
+    # without a CUDA library / GPU it must fail loudly, not fall back
+    r = subprocess.run([exe, "shirley", "45", "1", os.devnull], capture_output=True, text=True,
+                       env=dict(os.environ, SRT_B200_LIBRARY="/nonexistent/libsrt_b200.so"))
+    assert r.returncode != 0 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_example_renders_config1_like_the_library(tmp_path, device, dev_scenes, scenes):
+    """examples/sexy-raytracer shirley: scene built by the C++ classes, rendered through b200Device (dlopen of
+    libsrt_b200.so), written by srt_png_write == the frame srt_render gives for scenes/c1_shirley.npz (same seed)."""
+    from sexy_raytracer_b200 import build
+    exe = build.build_example()
+    out = str(tmp_path / "test.png")
+    r = subprocess.run([exe, "shirley", "225", "16", out], capture_output=True, text=True,
+                       env=dict(os.environ, SRT_B200_LIBRARY=build.LIB))
+    assert r.returncode == 0, r.stderr
+    got = host.png_read(out, 4)
+    s = scenes["c1_shirley"]
+    assert got.shape == (225, 400, 4)
+    _, want, _ = dev_scenes["c1_shirley"].render(s.render_params(width=400, height=225, spp=16, max_bounce=10, seed=1))
+    want = np.asarray(want).reshape(225, 400, 4)
+    assert (got[..., 3] == 255).all()
+    # the same kernels on the same description and seed: identical up to the order of the atomic adds of the accumulation
+    assert (np.abs(got.astype(int) - want.astype(int)) <= 1).mean() > 0.999
