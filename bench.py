@@ -308,12 +308,28 @@ def run_b200(args):
         # texel bytes belong to the shade kernel
         bps = 32 * k["B"] + 36 * k["Lt"] + 40 * k["Ls"] + 28
         kname = {1: "k_render_mega", 2: "k_wf_extend", 3: "k_render_phased"}.get(variant, "?")
+        in_smem = scene.nodes.nbytes + 32 <= 227 * 1024
+        note = ("algorithmic bytes are node/primitive/ray fetches of the traversal kernel; for this scene the nodes are served "
+                "from shared memory (whole BVH staged per CTA) and primitives from L1/L2, so DRAM traffic is far below "
+                "them and frac may exceed what HBM alone could deliver - see profiles/ and DESIGN.md 'Rooflines'") if in_smem else (
+                "tree in HBM: every lane reads one unpredictable 32-byte sector per step; the measured ceiling of the B200 for that "
+                "pattern is 40-50 G sectors/s (1.3-1.6 TB/s) beyond the L2 (tools/rand_access_bench.cu, profiles/r1_rand_access_b200.txt), "
+                "not the streaming peak - the walk over the compact 16-byte tree fetches fewer bytes than the algorithmic 32 per node")
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
+        # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel in this workload's launch shape,
+        # from the committed `ncu --set full` capture (profiles/r1_traffic.json names the report it was read from)
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(args.config)
+            if tr and tr.get("kernel") == kname and not args.spp and (args.config != "c5" or (args.tris, args.spheres) == (10_000_000, 100_000)):
+                traffic = tr["dram_bytes_per_launch"]
+        except (OSError, ValueError):
+            pass
         n_l = max(1, ext_launches)
         seg_rank0 = seg / n_l                                  # rank 0's segments (= rays traced) per launch of the dominant kernel
         launch_s = ext_ms / n_l * 1e-3                         # its average launch duration, CUDA events inside the timed region
@@ -324,15 +340,13 @@ def run_b200(args):
         fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
         roofline = {"kernel": kname, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak_hbm,
                     "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "unit": "GB/s",
-                    "frac": round(achieved / peak_hbm, 4), "traffic": None,
+                    "frac": round(achieved / peak_hbm, 4), "traffic": traffic,
                     "bytes_per_segment": round(bps, 1), "bytes_per_segment_whole_path": round(bps_all, 1),
                     "per_segment": {a: round(b, 3) for a, b in k.items()},
                     "segments_per_launch": round(seg_rank0, 1), "launch_ms": round(launch_s * 1e3, 4),
                     "launches_per_step": round(n_l / max(1, args.steps), 1),
                     "share_of_step": {kname: round(ext_ms / max(kern_ms, 1e-9), 4), "k_wf_shade": round(shd_ms / max(kern_ms, 1e-9), 4)},
-                    "note": "algorithmic bytes are node/primitive/ray fetches of the traversal kernel; for this scene the nodes are served "
-                            "from shared memory (whole BVH staged per CTA) and primitives from L1/L2, so DRAM traffic is far below "
-                            "them and frac may exceed what HBM alone could deliver - see profiles/ and DESIGN.md 'Rooflines'",
+                    "note": note,
                     "fp32": {"achieved_tflops": round(fl, 3), "peak_nominal_tflops": round(fp32_peak, 1),
                              "frac_fma_peak": round(fl / fp32_peak, 4), "frac_unfused_peak": round(fl / (fp32_peak / 2), 4),
                              "flops_per_segment": round(fl_seg, 1)}}

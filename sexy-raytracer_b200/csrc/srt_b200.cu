@@ -30,6 +30,7 @@ struct srt_device {
   int gpu = 0;
   int sm_count = 0;
   size_t smem_optin = 0;
+  size_t l2_bytes = 0;
   cudaStream_t stream = nullptr;       // the stream kernels are launched on
   cudaStream_t own_stream = nullptr;   // created by srt_device_create
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -85,6 +86,7 @@ srt_status srt_device_create(int gpu_id, srt_device** out) {
   CK(cudaGetDeviceProperties(&prop, gpu_id));
   d->sm_count = prop.multiProcessorCount;
   d->smem_optin = prop.sharedMemPerBlockOptin;
+  d->l2_bytes = (size_t)prop.l2CacheSize;
   CK(cudaStreamCreateWithFlags(&d->own_stream, cudaStreamNonBlocking));
   d->stream = d->own_stream;
   CK(cudaEventCreate(&d->ev0));
@@ -263,13 +265,68 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   const int n_real = (int)nodes.size();
   {  // sentinel at index n (not counted in n_nodes): a box-less leaf without primitives, see walk_step
     Node t; t.lo = make_float4(0, 0, 0, 0); t.hi = make_float4(0, 0, i2f(-1), i2f(NODE_NO_BOX));
-    nodes.push_back(t);
+    for (int k = 0; k < 4; k++) nodes.push_back(t);      // + 3 of padding: the walk may prefetch up to 3 nodes ahead
   }
   SCK(upload(s, nodes, &s->sc.nodes));
   s->sc.n_nodes = n_real;
   s->sc.filter_ok = filter_ok ? 1 : 0;
-  s->node_bytes = nodes.size() * sizeof(Node);
+  s->node_bytes = (size_t)(n_real + 1) * sizeof(Node);
   s->nodes_in_smem = s->node_bytes > 0 && s->node_bytes <= dev->smem_optin;
+  if (const char* f = getenv("SRT_FORCE_GLOBAL_TREE")) if (atoi(f)) s->nodes_in_smem = 0;   // tests: small scenes through the HBM paths
+
+  // compact tree + leaf-ordered primitives for trees that stay in HBM (srt_core.cuh)
+  std::vector<int32_t> lp_src;            // leaf order -> original primitive id
+  s->sc.cnodes = nullptr; s->sc.lprims = nullptr;
+  if (!s->nodes_in_smem && filter_ok && n_real > 0 && d->n_tri + d->n_sph < (int64_t)CNODE_NO_PRIM - 1) {
+    const Node& root = nodes[0];
+    const float rlo[3] = {root.lo.x, root.lo.y, root.lo.z}, rhi[3] = {root.lo.w, root.hi.x, root.hi.y};
+    double org[3], cell[3];
+    for (int k = 0; k < 3; k++) {
+      // float cell, rounded up so that 65534 cells span the root box; org is the root minimum itself
+      float c = (float)(((double)rhi[k] - (double)rlo[k]) / 65534.0);
+      c = std::nextafter(std::max(c, 1e-30f), std::numeric_limits<float>::infinity());
+      s->sc.q_org[k] = rlo[k]; s->sc.q_cell[k] = c;
+      org[k] = rlo[k]; cell[k] = c;
+    }
+    std::vector<uint4> cn(nodes.size());
+    auto snap = [&](double v, int k, bool up) -> uint32_t {
+      double g = (v - org[k]) / cell[k];
+      g = up ? std::ceil(g) : std::floor(g);
+      if (!(g >= 0.0)) g = 0.0;              // also NaN
+      if (g > 65535.0) g = 65535.0;
+      return (uint32_t)g;
+    };
+    bool ok = true;
+    for (size_t i = 0; i < nodes.size(); i++) {
+      const Node& nd = nodes[i];
+      int32_t w6, w7; memcpy(&w6, &nd.hi.z, 4); memcpy(&w7, &nd.hi.w, 4);
+      uint4 q = make_uint4(0, 0, 0, 0);
+      if (w7 != NODE_NO_BOX) {
+        const float lo[3] = {nd.lo.x, nd.lo.y, nd.lo.z}, hi[3] = {nd.lo.w, nd.hi.x, nd.hi.y};
+        uint32_t L[3], H[3];
+        for (int k = 0; k < 3; k++) {
+          // a box outside the root box (malformed tree) cannot be snapped conservatively: keep the 32-byte path
+          if (!(lo[k] >= rlo[k]) || !(hi[k] <= rhi[k])) ok = false;
+          L[k] = snap(lo[k], k, false); H[k] = snap(hi[k], k, true);
+        }
+        q.x = L[0] | (L[1] << 16); q.y = L[2] | (H[0] << 16); q.z = H[1] | (H[2] << 16);
+      }
+      if (w7 == NODE_INNER) q.w = CNODE_INNER | (uint32_t)w6;
+      else {
+        uint32_t w = w7 == NODE_NO_BOX ? CNODE_NO_BOX : 0u;
+        if (w6 < 0) w |= CNODE_NO_PRIM;                                        // the sentinel
+        else {
+          w |= (uint32_t)lp_src.size();
+          lp_src.push_back(w6);
+          if (w7 >= 0) { w |= CNODE_TWO; lp_src.push_back(w7); }
+        }
+        q.w = w;
+      }
+      cn[i] = q;
+    }
+    if (ok) SCK(upload(s, cn, &s->sc.cnodes));
+    else lp_src.clear();
+  }
 
   std::vector<Tri> tris((size_t)d->n_tri);
   std::vector<TriUV> uvs((size_t)d->n_tri);
@@ -354,6 +411,24 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     k_setup_tris<<<(unsigned)((d->n_tri + 255) / 256), 256, 0, dev->stream>>>(const_cast<Tri*>(s->sc.tris), (int)d->n_tri);
     cudaError_t e = cudaStreamSynchronize(dev->stream);
     if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("k_setup_tris: ") + cudaGetErrorString(e)); }
+  }
+  if (s->sc.cnodes && !lp_src.empty()) {       // leaf-ordered copies of the (set-up) primitives
+    const int32_t* d_src = nullptr;
+    srt_status rc2 = upload(s, lp_src, &d_src);
+    void* lp = nullptr;
+    if (!rc2) {
+      cudaError_t e = cudaMalloc(&lp, lp_src.size() * sizeof(LPrim));
+      if (e != cudaSuccess) { cudaGetLastError(); rc2 = fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
+    }
+    if (rc2) { srt_scene_destroy(s); return rc2; }
+    s->buffers.push_back(lp);
+    s->bytes += (int64_t)(lp_src.size() * sizeof(LPrim));
+    k_build_lprims<<<(unsigned)((lp_src.size() + 255) / 256), 256, 0, dev->stream>>>(s->sc, d_src, (int)lp_src.size(), static_cast<LPrim*>(lp));
+    cudaError_t e = cudaStreamSynchronize(dev->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("k_build_lprims: ") + cudaGetErrorString(e)); }
+    s->sc.lprims = static_cast<const LPrim*>(lp);
+  } else {
+    s->sc.cnodes = nullptr;
   }
   *out = s;
   return SRT_OK;

@@ -80,7 +80,32 @@ struct Mat {
   float fuzz, ir, pad0, pad1;
 };
 
+// ---- compact tree (trees that do not fit shared memory; BASELINE config 5) ---------------------------------------
+// A second, 16-byte image of every node for the walk in global memory, where the cost of a step is the number of
+// 32-byte sectors it pulls from HBM (profiles/r1_c5_extend_summary.md): the box snapped OUTWARD to a 16-bit grid over
+// the root box (6 x uint16) + one word.  Two nodes share a sector, and node i+1 - the left child, next in pre-order -
+// is the other half of node i's sector every second time.
+//   q.x = lo.x | lo.y << 16    q.y = lo.z | hi.x << 16    q.z = hi.y | hi.z << 16
+//   q.w : bit 31 set   -> inner node, bits 0-30 = skip index
+//         bit 31 clear -> leaf: bits 0-28 = index u of its first primitive in the LEAF-ORDERED primitive array
+//                         (CNODE_NO_PRIM = none: the sentinel), bit 29 = a second primitive follows at u + 1,
+//                         bit 30 = the node has no box (a primitive hanging directly under an inner node)
+// The snapped box only FILTERS: with outer = [lo, hi] cells and inner = [lo + 1, hi - 1] cells,
+//   ray misses outer  => misses the true box;   ray hits inner => hits the true box   (slab intervals are nested),
+// both decided with a rounding margin; the thin shell in between (a few % of the tests) and every ray the filter
+// cannot serve re-evaluates aabb::hit on the full 32-byte node with the reference's arithmetic.
+#define CNODE_INNER   0x80000000u
+#define CNODE_TWO     0x20000000u
+#define CNODE_NO_BOX  0x40000000u
+#define CNODE_NO_PRIM 0x1fffffffu
+// leaf-ordered primitive record, 64 bytes: a triangle as Tri with d = (dd, mat, original id, 0), or a sphere as
+// (Sph.a, Sph.b, Sph.c, d = (-, mat, original id, 1)) - the two primitives of a leaf are neighbours in memory
+struct LPrim { float4 a, b, c, d; };
+
 struct Scene {
+  const uint4* cnodes;   // compact tree, or nullptr
+  const LPrim* lprims;
+  float q_org[3], q_cell[3];
   const Node*  nodes;  int n_nodes;
   const Tri*   tris;   int n_tri;
   const TriUV* tri_uv;
@@ -196,6 +221,121 @@ __device__ __forceinline__ bool sph_hit(const Sph* __restrict__ sphs, int j, con
 }
 
 struct Counters { unsigned long long nodes, leaves, exact, sph_leaves, tri_hits; };
+
+// ---- compact-node box filter -------------------------------------------------------------------------------------
+// Slab bounds of the snapped box: t(q) = ((org + q cell) - o) / d = fma(q, cid, c0) with cid = fl(cell id), id = fl(1/d),
+// c0 = fl(fl(org - o) id).  |t_computed - t_real| <= 3u Mq + u|t| (u = 2^-24, Mq = max_k |c0_k| + 65535 |cid_k|); the
+// reference's own fl(fl(c - o) / d) is within 2u|t| of the real quotient.  Both decisions keep a margin of
+// 2^-19 (Mq + |l| + |h|) + 1e-30 - more than 5x the sum of those bounds.
+struct RayAuxC { float cx, cy, cz, kx, ky, kz, Mq; int ok; };
+
+__device__ __forceinline__ RayAuxC make_aux_c(const Scene& sc, const Ray& r) {
+  RayAuxC a;
+  const float idx = 1.0f / r.d.x, idy = 1.0f / r.d.y, idz = 1.0f / r.d.z;
+  a.cx = sc.q_cell[0] * idx; a.cy = sc.q_cell[1] * idy; a.cz = sc.q_cell[2] * idz;
+  a.kx = (sc.q_org[0] - r.o.x) * idx; a.ky = (sc.q_org[1] - r.o.y) * idy; a.kz = (sc.q_org[2] - r.o.z) * idz;
+  a.Mq = fmaxf(fmaf(65535.0f, fabsf(a.cx), fabsf(a.kx)), fmaxf(fmaf(65535.0f, fabsf(a.cy), fabsf(a.ky)), fmaf(65535.0f, fabsf(a.cz), fabsf(a.kz))));
+  const float mi = fmaxf(fabsf(idx), fmaxf(fabsf(idy), fabsf(idz)));
+  a.ok = (mi <= 1.0995116e12f) && (a.Mq <= 1.1529215e18f) && (r.time == r.time);    // false for NaN / inf / zero components
+  if (!a.ok) a.Mq = __int_as_float(0x7f800000);          // the margin becomes infinite: every test goes to the exact path
+  return a;
+}
+
+// -> +1 certain hit, -1 certain miss, 0 undecided
+__device__ __forceinline__ int cbox_filter(const uint4& q, const RayAuxC& x, float tMin, float tCur) {
+  const float lx = __uint2float_rn(q.x & 0xffffu), ly = __uint2float_rn(q.x >> 16), lz = __uint2float_rn(q.y & 0xffffu);
+  const float hx = __uint2float_rn(q.y >> 16), hy = __uint2float_rn(q.z & 0xffffu), hz = __uint2float_rn(q.z >> 16);
+  const float ax = fmaf(lx, x.cx, x.kx), bx = fmaf(hx, x.cx, x.kx);
+  const float ay = fmaf(ly, x.cy, x.ky), by = fmaf(hy, x.cy, x.ky);
+  const float az = fmaf(lz, x.cz, x.kz), bz = fmaf(hz, x.cz, x.kz);
+  const float nx = fminf(ax, bx), ny = fminf(ay, by), nz = fminf(az, bz);
+  const float fx = fmaxf(ax, bx), fy = fmaxf(ay, by), fz = fmaxf(az, bz);
+  const float lo = fmaxf(fmaxf(nx, ny), fmaxf(nz, tMin)), ho = fminf(fminf(fx, fy), fminf(fz, tCur));
+  const float ex = fabsf(x.cx), ey = fabsf(x.cy), ez = fabsf(x.cz);
+  const float li = fmaxf(fmaxf(nx + ex, ny + ey), fmaxf(nz + ez, tMin)), hi = fminf(fminf(fx - ex, fy - ey), fminf(fz - ez, tCur));
+  const float slack = fmaf(1.9073486e-6f, x.Mq + fabsf(lo) + fabsf(ho), 1e-30f);
+  if ((ho - lo) < -slack) return -1;
+  if ((hi - li) > slack) return 1;
+  return 0;
+}
+
+// one primitive of the leaf-ordered array against the ray (same decisions as tri_hit / sph_hit); `orig` = its id
+__device__ __forceinline__ bool lprim_hit(const LPrim* __restrict__ lp, unsigned u, const Ray& r, float tMin, float tCur, float& tOut,
+                                          int& orig, bool& is_sphere) {
+  const float4 A = __ldg(&lp[u].a), B = __ldg(&lp[u].b), C = __ldg(&lp[u].c), D = __ldg(&lp[u].d);
+  orig = __float_as_int(D.z);
+  is_sphere = __float_as_int(D.w) != 0;
+  if (is_sphere) {
+    V3 oc = r.o - sph_center(A, B, C, r.time);
+    float aa = length_squared(r.d);
+    float halfB = dot(oc, r.d);
+    float cc = length_squared(oc) - A.w * A.w;
+    float disc = halfB * halfB - aa * cc;
+    if (disc < 0.0f) return false;
+    float sqrtd = sqrtf(disc);
+    float root = (-halfB - sqrtd) / aa;
+    if (root < tMin || root > tCur) {
+      root = (-halfB + sqrtd) / aa;
+      if (root < tMin || root > tCur) return false;
+    }
+    tOut = root;
+    return true;
+  }
+  V3 N = mk(A.w, B.w, C.w);
+  float NdotDir = dot(N, r.d);
+  if (fabsf(NdotDir) < FLT_EPSILON) return false;
+  if (NdotDir > 0) return false;
+  float t = -(dot(N, r.o) + D.x) / NdotDir;
+  if (t < tMin) return false;
+  V3 v0 = mk(A.x, A.y, A.z), v1 = mk(B.x, B.y, B.z), v2 = mk(C.x, C.y, C.z);
+  V3 p = mk(r.o.x + t * r.d.x, r.o.y + t * r.d.y, r.o.z + t * r.d.z);
+  if (dot(N, cross(v1 - v0, p - v0)) < 0) return false;
+  if (dot(N, cross(v2 - v1, p - v1)) < 0) return false;
+  if (dot(N, cross(v0 - v2, p - v2)) < 0) return false;
+  tOut = t;
+  return true;
+}
+
+// hittableList::hit over the compact tree: the same walk as traverse() below (pre-order, running tCur, every accept
+// overwrites), node decisions through cbox_filter with the exact fallback on the full node.
+template <bool COUNT>
+__device__ __forceinline__ void traverse_compact(const Scene& sc, const Ray& r, float tMin, float tMax, int& prim, float& tHit,
+                                                 Counters* cnt) {
+  const RayAuxC aux = make_aux_c(sc, r);
+  float tCur = tMax;
+  prim = -1;
+  int i = 0;
+  const int n = sc.n_nodes;
+  while (i < n) {
+    const uint4 q = __ldg(&sc.cnodes[i]);
+    if (COUNT) ++cnt->nodes;
+    bool hit = true;
+    if (!(q.w & CNODE_NO_BOX) || (q.w & CNODE_INNER)) {
+      const int f = cbox_filter(q, aux, tMin, tCur);
+      if (f == 0) {
+        if (COUNT) ++cnt->exact;
+        hit = box_hit_exact(__ldg(&sc.nodes[i].lo), __ldg(&sc.nodes[i].hi), r, tMin, tCur);
+      } else hit = f > 0;
+    }
+    if (q.w & CNODE_INNER) {
+      i = hit ? i + 1 : (int)(q.w & 0x7fffffffu);
+    } else {
+      const unsigned u = q.w & CNODE_NO_PRIM;
+      if (hit && u != CNODE_NO_PRIM) {
+        const int cntp = (q.w & CNODE_TWO) ? 2 : 1;
+#pragma unroll 1
+        for (int k = 0; k < cntp; k++) {
+          float t; int orig; bool sph;
+          const bool acc = lprim_hit(sc.lprims, u + k, r, tMin, tCur, t, orig, sph);
+          if (COUNT) { ++cnt->leaves; if (sph) ++cnt->sph_leaves; }
+          if (acc) { tCur = t; prim = orig; }
+        }
+      }
+      i = i + 1;
+    }
+  }
+  tHit = tCur;
+}
 
 // hittableList::hit -> bvhNode::hit (hittablelist.h:33-47, bvh.h:97-105) in the threaded form.
 // Rule: walk in pre-order; one running tCur = t of the most recently ACCEPTED leaf

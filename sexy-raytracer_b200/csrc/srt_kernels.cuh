@@ -19,6 +19,22 @@ __global__ void k_setup_tris(Tri* tris, int n) {
   tris[i].a.w = N.x; tris[i].b.w = N.y; tris[i].c.w = N.z; tris[i].d.x = dd;
 }
 
+// leaf-ordered copies of the primitives for the compact tree (srt_core.cuh: LPrim); runs after k_setup_tris
+__global__ void k_build_lprims(Scene sc, const int32_t* __restrict__ src, int n, LPrim* __restrict__ out) {
+  int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n) return;
+  const int p = src[u];
+  LPrim r;
+  if (p < sc.n_tri) {
+    const Tri t = sc.tris[p];
+    r.a = t.a; r.b = t.b; r.c = t.c; r.d = make_float4(t.d.x, t.d.y, __int_as_float(p), __int_as_float(0));
+  } else {
+    const Sph q = sc.sphs[p - sc.n_tri];
+    r.a = q.a; r.b = q.b; r.c = q.c; r.d = make_float4(0.0f, q.c.y, __int_as_float(p), __int_as_float(1));
+  }
+  out[u] = r;
+}
+
 __device__ __forceinline__ Ray load_ray(const srt_ray* q) {
   Ray r;
   r.o = mk(q->o[0], q->o[1], q->o[2]); r.d = mk(q->dir[0], q->dir[1], q->dir[2]); r.time = q->time;
@@ -47,7 +63,8 @@ __global__ void __launch_bounds__(256) k_trace_rays(Scene sc, int nodes_in_smem,
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     Ray r = load_ray(&rays[i]);
     int prim; float t;
-    traverse<COUNT>(sc, nodes, r, tMin, tMax, prim, t, &cnt);
+    if (sc.cnodes && !nodes_in_smem) traverse_compact<COUNT>(sc, r, tMin, tMax, prim, t, &cnt);   // big trees: the compact walk
+    else traverse<COUNT>(sc, nodes, r, tMin, tMax, prim, t, &cnt);
     srt_hit h;
     if (prim < 0) {
       h.prim = -1; h.mat = -1; h.front_face = 0; h.t = 0;

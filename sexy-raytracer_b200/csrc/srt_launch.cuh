@@ -17,9 +17,9 @@ struct RenderPlan {
 
 typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
 template <int THREADS>
-extend_fn pick_extend(bool count, bool smem) {
-  if (count) return smem ? k_wf_extend<true, true, THREADS> : k_wf_extend<true, false, THREADS>;
-  return smem ? k_wf_extend<false, true, THREADS> : k_wf_extend<false, false, THREADS>;
+extend_fn pick_extend(bool count, int mode) {     // mode 0: tree in shared memory, 1: 32-byte nodes in HBM, 2: compact tree in HBM
+  if (count) return mode == 0 ? k_wf_extend<true, 0, THREADS> : mode == 1 ? k_wf_extend<true, 1, THREADS> : k_wf_extend<true, 2, THREADS>;
+  return mode == 0 ? k_wf_extend<false, 0, THREADS> : mode == 1 ? k_wf_extend<false, 1, THREADS> : k_wf_extend<false, 2, THREADS>;
 }
 
 // variant 1: k_render_mega (flat per-lane loop); variant 3: k_render_phased (warp-voted phases); 0 = auto = 3
@@ -67,10 +67,18 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
     }
     const long long total = (long long)A.n_tiles * 32 * A.sample_count;
     if ((long long)plan.wf_slots > total) plan.wf_slots = (int)((total + 255) / 256 * 256);
-    extend_fn fn = plan.threads == 1024 ? pick_extend<1024>(dev->counters, s->nodes_in_smem)
-                   : plan.threads == 768 ? pick_extend<768>(dev->counters, s->nodes_in_smem)
-                   : plan.threads == 256 ? pick_extend<256>(dev->counters, s->nodes_in_smem)
-                                         : pick_extend<512>(dev->counters, s->nodes_in_smem);
+    // Trees in HBM: the compact tree pays off once the 32-byte nodes no longer fit the L2 (config 5: 378 MB of nodes,
+    // 47.6 vs 36.7 M segments/s); an L2-resident tree is faster through its full nodes (1 M triangles: 236 vs 221).
+    // SRT_WF_TREE=full|compact overrides (A/B measurements, tests).
+    const char* tree = getenv("SRT_WF_TREE");
+    bool compact = s->sc.cnodes && s->node_bytes > dev->l2_bytes;
+    if (tree && !strcmp(tree, "full")) compact = false;
+    if (tree && !strcmp(tree, "compact")) compact = s->sc.cnodes != nullptr;
+    const int mode = s->nodes_in_smem ? 0 : compact ? 2 : 1;
+    extend_fn fn = plan.threads == 1024 ? pick_extend<1024>(dev->counters, mode)
+                   : plan.threads == 768 ? pick_extend<768>(dev->counters, mode)
+                   : plan.threads == 256 ? pick_extend<256>(dev->counters, mode)
+                                         : pick_extend<512>(dev->counters, mode);
     plan.fn = (const void*)fn;
     plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
     e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);

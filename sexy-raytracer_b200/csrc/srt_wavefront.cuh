@@ -52,8 +52,8 @@ __device__ __forceinline__ void load_node_soa(const Node* nodes, uint32_t nodes_
     const uint32_t a = nodes_s + (uint32_t)i * 16u;
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w) : "r"(a));
     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "r"(a + hi_off));
-  } else {
-    lo = __ldg(&nodes[i].lo); hi = __ldg(&nodes[i].hi);
+  } else {     // one 256-bit load: a node is one 32-byte sector
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "l"(nodes + i));
   }
 }
 
@@ -91,10 +91,33 @@ __device__ __forceinline__ void walk_step(const Node* nodes, uint32_t nodes_s, u
   i = (hit && !inner) ? ~i : next;
 }
 
+// The same step over the compact tree (srt_core.cuh): one 16-byte load, the snapped-box filter, and the reference's
+// arithmetic on the full node only for the undecided shell.
+// An undecided test does NOT run here: a dependent HBM round trip for one or two lanes would stall the whole warp on
+// ~40 % of its steps (profiles/r1_c5_extend_summary.md).  The lane stops on the node with `pend` set, the full node is
+// prefetched, and the service phase evaluates aabb::hit together with the other stopped lanes.
+template <bool COUNT>
+__device__ __forceinline__ void walk_step_c(const Scene& sc, int n, const RayAuxC& x, int& i, bool& pend, float tCur, Counters& cnt) {
+  const uint4 q = __ldg(&sc.cnodes[i]);
+  if (COUNT && i < n) ++cnt.nodes;
+  const bool inner = (q.w & CNODE_INNER) != 0;
+  const bool nobox = !inner && (q.w & CNODE_NO_BOX);
+  const int f = cbox_filter(q, x, 0.001f, tCur);
+  const bool und = f == 0 && !nobox;
+  const bool hit = f > 0 || nobox;
+  if (und) { pend = true; asm volatile("prefetch.global.L2 [%0];" :: "l"(sc.nodes + i)); }
+  const int next = (inner && !hit) ? (int)(q.w & 0x7fffffffu) : i + 1;
+  i = (und || (hit && !inner)) ? ~i : next;
+}
+
 // ---- EXTEND ------------------------------------------------------------------------------------------
-template <bool COUNT, bool SMEM, int THREADS>
-__global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
+// MODE 0: tree staged in shared memory; 1: 32-byte nodes in global memory; 2: compact tree in global memory
+template <bool COUNT, int MODE, int THREADS>
+__global__ void __launch_bounds__(THREADS, (MODE != 0 && THREADS <= 512) ? 1536 / THREADS : (MODE != 0 && THREADS == 768) ? 2 : 1)
+k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
                                                           unsigned long long* counters) {
+  constexpr bool SMEM = MODE == 0;
+  constexpr bool CPT = MODE == 2;
   extern __shared__ float4 smem_nodes[];
   const Node* nodes = sc.nodes;
   if (SMEM) stage_nodes_soa(sc, smem_nodes);
@@ -108,10 +131,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
 
   Ray r; r.o = r.d = mk(0, 0, 0); r.time = 0;
   RayAux aux = make_aux(r, 0);
+  RayAuxC auxc = {0, 0, 0, 0, 0, 0, 0, 0};
   const uint32_t nodes_s = SMEM ? (uint32_t)__cvta_generic_to_shared(smem_nodes) : 0u;
   int slot = -1;                   // -1: this lane holds no ray
   int i = -1, prim = -1;           // i >= 0: walking, next node i;  i < 0 with a slot: stopped on node ~i (hit leaf, or sentinel = done)
   float tCur = INF;
+  bool pend = false;               // compact tree: stopped on node ~i whose snapped box could not decide - aabb::hit is due
   bool pool_dry = false;           // warp-uniform: the wave's rays are all handed out
 
   for (;;) {
@@ -121,6 +146,30 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
       if (at >= n) {
         pool.hit[slot] = make_int2(prim, __float_as_int(tCur));
         slot = -1;
+      } else if (CPT) {
+        const unsigned w = __ldg(&sc.cnodes[at].w);
+        bool go = true;                           // the leaf's box is hit: test its primitives
+        if (pend) {                               // the reference's own arithmetic on the full node
+          pend = false;
+          float4 lo, hi;
+          load_node_soa<false>(nodes, 0u, 0u, at, lo, hi);
+          if (COUNT) ++cnt.exact;
+          go = box_hit_exact(lo, hi, r, 0.001f, tCur);
+          if (w & CNODE_INNER) { i = go ? at + 1 : (int)(w & 0x7fffffffu); go = false; }
+          else if (!go) i = at + 1;
+        }
+        if (go) {
+          const unsigned u = w & CNODE_NO_PRIM;
+          const int np = u == CNODE_NO_PRIM ? 0 : ((w & CNODE_TWO) ? 2 : 1);
+#pragma unroll 1
+          for (int k = 0; k < np; k++) {
+            float t; int orig; bool sph;
+            const bool acc = lprim_hit(sc.lprims, u + k, r, 0.001f, tCur, t, orig, sph);
+            if (COUNT) { ++cnt.leaves; if (sph) ++cnt.sph_leaves; }
+            if (acc) { tCur = t; prim = orig; }
+          }
+          i = at + 1;
+        }
       } else {
         float4 lo, hi;
         load_node_soa<SMEM>(nodes, nodes_s, hi_off, at, lo, hi);
@@ -153,9 +202,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
             if (__float_as_int(d.w) == 1) {
               slot = (int)mine;
               r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
-              aux = make_aux(r, sc.filter_ok);
-              if (!aux.ok) aux.M = INF;          // walk_step then always takes the exact test
-              i = 0; tCur = INF; prim = -1;
+              if (CPT) auxc = make_aux_c(sc, r);
+              else {
+                aux = make_aux(r, sc.filter_ok);
+                if (!aux.ok) aux.M = INF;        // walk_step then always takes the exact test
+              }
+              i = 0; tCur = INF; prim = -1; pend = false;
             }
           }
         }
@@ -171,7 +223,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend(Scene sc, WfPool pool,
     do {
 #pragma unroll
       for (int rep = 0; rep < 2; rep++)     // two steps per vote
-        if (i >= 0) walk_step<COUNT, SMEM>(nodes, nodes_s, hi_off, n, r, aux, i, tCur, cnt);
+        if (i >= 0) {
+          if (CPT) walk_step_c<COUNT>(sc, n, auxc, i, pend, tCur, cnt);
+          else walk_step<COUNT, SMEM>(nodes, nodes_s, hi_off, n, r, aux, i, tCur, cnt);
+        }
     } while (__popc(__ballot_sync(FULL, i >= 0)) >= th_walk);
   }
 

@@ -325,3 +325,70 @@ def test_errors_are_loud(device, scenes):
     with pytest.raises(SrtError):
         ds.render(s.render_params(width=1))
     ds.close()
+
+
+# ---- trees that stay in HBM: the compact 16-byte tree + leaf-ordered primitives (srt_core.cuh), and the 32-byte nodes ----
+@pytest.fixture(scope="module")
+def hbm_scenes(device, scenes):
+    """The four reference scenes uploaded with their tree kept OUT of shared memory (SRT_FORCE_GLOBAL_TREE), which is
+    what a tree beyond 227 KB gets (BASELINE config 5): srt_trace_rays and k_wf_extend then walk the compact tree."""
+    import os
+    os.environ["SRT_FORCE_GLOBAL_TREE"] = "1"
+    try:
+        out = {n: device.upload(s) for n, s in scenes.items()}
+    finally:
+        del os.environ["SRT_FORCE_GLOBAL_TREE"]
+    yield out
+    for s in out.values():
+        s.close()
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_compact_tree_trace_vs_reference_golden(name, hbm_scenes, golden):
+    """Same bar as the shared-memory path: ids bit-exact against the compiled reference on every golden ray set - the
+    snapped-box filter may never change a decision."""
+    g = golden.kat(name)
+    for k in SETS:
+        check_hits(hbm_scenes[name].trace(g["rays_" + k]), g["hits_" + k])
+    check_hits(hbm_scenes[name].trace(g["rays_bounded"], 0.05, 0.9), g["hits_bounded"])
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_compact_tree_counters_and_fallback_rate(name, device, hbm_scenes, dev_scenes, golden):
+    g = golden.kat(name)
+    device.set_counters(True)
+    try:
+        hbm_scenes[name].trace(g["rays_secondary"])
+        c = device.last_counters()
+        dev_scenes[name].trace(g["rays_secondary"])
+        c0 = device.last_counters()
+    finally:
+        device.set_counters(False)
+    box, leaf = (int(x) for x in g["count_secondary"])
+    assert c["node_visits"] == box == c0["node_visits"]
+    assert c["leaf_tests"] == c0["leaf_tests"] and c["sphere_leaf_tests"] == c0["sphere_leaf_tests"]
+    # the undecided shell of the snapped boxes: a minority of the tests even on these small scenes (the 1000-unit ground
+    # sphere stretches the grid of the default scene to 0.03 units per cell)
+    assert c["exact_box_tests"] < 0.35 * box
+
+
+@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("tree", ["compact", "full"])
+def test_hbm_tree_wavefront_agrees(name, tree, hbm_scenes, dev_scenes, scenes):
+    """k_wf_extend over the compact tree (MODE 2) and over the 32-byte nodes in HBM (MODE 1) trace the same paths as the
+    megakernel over the shared-memory tree."""
+    import os
+    s = scenes[name]
+    W, H, spp = SMALL[name]
+    kw = dict(width=W, height=H, spp=spp, seed=11)
+    a, ra, sa = dev_scenes[name].render(s.render_params(variant=1, **kw))
+    os.environ["SRT_WF_TREE"] = tree
+    try:
+        b, rb, sb = hbm_scenes[name].render(s.render_params(variant=2, **kw))
+    finally:
+        del os.environ["SRT_WF_TREE"]
+    assert sa.paths == sb.paths and sa.segments == sb.segments
+    fin = np.isfinite(a).all(axis=2)
+    assert (np.isfinite(b).all(axis=2) == fin).all()
+    assert np.abs(a[fin] - b[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max())
+    assert (np.abs(ra.astype(int) - rb.astype(int)) <= 1).all()
