@@ -159,7 +159,7 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
   void* extend_args[] = {&sc, &pool, &cur, &th_walk, &ctr};
   const unsigned reset_blocks = (unsigned)((N + 255) / 256);
-  unsigned shade_blocks = (unsigned)dev->sm_count * 6;            // persistent: 3 resident CTAs per SM, two rounds
+  unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS;   // persistent: resident CTAs per SM x two rounds
   if (shade_blocks > reset_blocks) shade_blocks = reset_blocks;
   int launches = 0;
 

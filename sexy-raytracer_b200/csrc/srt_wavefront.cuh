@@ -244,6 +244,9 @@ k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
   }
 }
 
+#ifndef SRT_SHADE_MIN_BLOCKS
+#define SRT_SHADE_MIN_BLOCKS 4   /* 64 registers, 52 B of spills: 4 CTAs per SM measured +3-4 % per frame over 3 (80 registers) */
+#endif
 // ---- SHADE + REGENERATE ----------------------------------------------------------------------------
 // One thread per slot, persistent blocks striding over 256-slot chunks.  The frame's paths are numbered
 // 0 .. n_tiles*32*sample_count-1: path id -> (sample offset, 8x4 tile, pixel of the tile), so that slots
@@ -252,7 +255,7 @@ k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
 // statistics stay in registers until the block ends.
 // counters: [0] paths, [1] segments, [7] segments that ended on a triangle (COUNT only)
 template <bool COUNT>
-__global__ void __launch_bounds__(256) k_wf_shade(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
+__global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
                                                   unsigned long long* counters) {
   __shared__ unsigned s_cnt[8];
   __shared__ unsigned long long s_base;

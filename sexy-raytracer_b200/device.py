@@ -9,7 +9,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsrt_b200.so")
+LIB_PATH = os.environ.get("SRT_B200_LIBRARY") or os.path.join(_HERE, "libsrt_b200.so")   # the override is for A/B builds (tools/)
 _lib = None
 
 
