@@ -12,7 +12,7 @@ struct DevBuf {   // scoped device allocation
 
 struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
-  int wf_slots, wf_th_walk; const void* wf_shade;     // variant 2
+  int wf_slots, wf_th_walk, wf_shade_chunk; const void* wf_shade;     // variant 2
 };
 
 typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
@@ -80,7 +80,13 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
                    : plan.threads == 256 ? pick_extend<256>(dev->counters, mode)
                                          : pick_extend<512>(dev->counters, mode);
     plan.fn = (const void*)fn;
-    plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
+    {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
+      const char* sh = getenv("SRT_WF_SHADE");
+      const bool sorted = !(sh && atoi(sh) == 1);
+      plan.wf_shade_chunk = sorted ? 512 : 256;
+      plan.wf_shade = sorted ? (dev->counters ? (const void*)k_wf_shade2<true> : (const void*)k_wf_shade2<false>)
+                             : (dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>);
+    }
     e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
   } else if (plan.variant == 3) {
@@ -160,7 +166,10 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   void* extend_args[] = {&sc, &pool, &cur, &th_walk, &ctr};
   const unsigned reset_blocks = (unsigned)((N + 255) / 256);
   unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS;   // persistent: resident CTAs per SM x two rounds
-  if (shade_blocks > reset_blocks) shade_blocks = reset_blocks;
+  {
+    const unsigned chunks = (unsigned)((N + plan.wf_shade_chunk - 1) / plan.wf_shade_chunk);
+    if (shade_blocks > chunks) shade_blocks = chunks;
+  }
   int launches = 0;
 
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));

@@ -16,6 +16,14 @@
 #pragma once
 #include "srt_phased.cuh"
 
+// build-time tuning switches (A/B builds: tools/b.sh -DSRT_...=...)
+#ifndef SRT_FMNMX3
+#define SRT_FMNMX3 0
+#endif
+#ifndef SRT_WALK_REPS
+#define SRT_WALK_REPS 2
+#endif
+
 namespace srt {
 
 struct WfPool {
@@ -75,8 +83,15 @@ __device__ __forceinline__ void walk_step(const Node* nodes, uint32_t nodes_s, u
   const float ax = fmaf(lo.x, x.idx, -x.oidx), bx = fmaf(lo.w, x.idx, -x.oidx);
   const float ay = fmaf(lo.y, x.idy, -x.oidy), by = fmaf(hi.x, x.idy, -x.oidy);
   const float az = fmaf(lo.z, x.idz, -x.oidz), bz = fmaf(hi.y, x.idz, -x.oidz);
+#if SRT_FMNMX3
+  // three-input min/max (FMNMX3 on sm_100a; NaN -> the other operands, like fminf/fmaxf): 10 instead of 12 on the ALU pipe
+  float l, h;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(l) : "f"(fminf(ax, bx)), "f"(fminf(ay, by)), "f"(fmaxf(fminf(az, bz), 0.001f)));
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(h) : "f"(fmaxf(ax, bx)), "f"(fmaxf(ay, by)), "f"(fminf(fmaxf(az, bz), tCur)));
+#else
   const float l = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.001f));
   const float h = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tCur));
+#endif
   const float slack = fmaf(9.5367432e-7f, x.M + fabsf(l) + fabsf(h), 1e-30f);   // x.M = +inf when the filter is off
   const float diff = h - l;
   bool hit = diff > 0.0f;
@@ -222,7 +237,7 @@ k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
     }
     do {
 #pragma unroll
-      for (int rep = 0; rep < 2; rep++)     // two steps per vote
+      for (int rep = 0; rep < SRT_WALK_REPS; rep++)     // steps per vote
         if (i >= 0) {
           if (CPT) walk_step_c<COUNT>(sc, n, auxc, i, pend, tCur, cnt);
           else walk_step<COUNT, SMEM>(nodes, nodes_s, hi_off, n, r, aux, i, tCur, cnt);
@@ -351,6 +366,132 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
   if (threadIdx.x == 0) {
     if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
     if (s_stat[1]) { atomicAdd(&counters[1], s_stat[1]); cur->alive = 1; }     // flag, not a count
+    if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
+  }
+}
+
+// ---- SHADE + REGENERATE, sorted phases --------------------------------------------------------------------------
+// k_wf_shade runs one thread per slot: after a wave ~45 % of the slots hold a miss (a dozen instructions), ~55 % a hit
+// (emitted + scatter + textures, ~450) and more than half of them then regenerate (two Philox blocks + camera::getRay) -
+// 16 of 32 lanes active on average (profiles/r1_wavefront_summary.md).  Here a block takes 512 slots at a time and runs the
+// three jobs as separate passes over COMPACTED index lists in shared memory, so every pass runs with full warps:
+//   pass 0  (thread = slot)      : classify; misses add the background and retire at once; hits are listed
+//   pass 1  (thread = list item) : shade_segment for the listed hits; paths that end retire
+//   pass 2  (thread = list item) : retired / empty slots take the next path ids of the frame and generate their ray
+// Same arithmetic, same Philox keys; only which thread serves which slot and the order paths are numbered change.
+template <bool COUNT>
+__global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
+                                                   unsigned long long* counters) {
+  constexpr int CH = 512;
+  __shared__ unsigned short s_hit[CH], s_free[CH];
+  __shared__ unsigned s_nhit, s_nfree;
+  __shared__ unsigned long long s_base;
+  __shared__ unsigned long long s_stat[3];
+  const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu;
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur->ray = 0;    // the next extend wave starts at slot 0
+  if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+  const unsigned long long per_sample = (unsigned long long)A.n_tiles * 32ull;
+  const unsigned long long total = per_sample * (unsigned long long)A.sample_count;
+  Counters cnt = {0, 0, 0, 0, 0};
+  unsigned n_new = 0, n_seg = 0;
+
+  for (int chunk = blockIdx.x; chunk * CH < pool.n_slots; chunk += gridDim.x) {
+    const int base = chunk * CH;
+    if (threadIdx.x == 0) { s_nhit = 0; s_nfree = 0; }
+    __syncthreads();
+    // ---- pass 0: classify (two slots per thread)
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const int j = q * 256 + threadIdx.x, k = base + j;
+      bool is_hit = false, is_free = false;
+      if (k < pool.n_slots) {
+        const float4 t4 = pool.thr[k];
+        const int2 h = pool.hit[k];
+        if (__float_as_int(t4.w) < 0) is_free = true;                      // no path in this slot
+        else if (h.x < 0) {                                                // miss -> background, main.cpp:39-40
+          const float4 l4 = pool.rad[k];
+          const uint32_t pixel = pool.id[k].x;
+          float* px = accum + (size_t)pixel * 3;
+          atomicAdd(px, l4.x + t4.x * A.bg[0]); atomicAdd(px + 1, l4.y + t4.y * A.bg[1]); atomicAdd(px + 2, l4.z + t4.z * A.bg[2]);
+          is_free = true;
+        } else is_hit = true;
+      }
+      const unsigned mh = __ballot_sync(FULL, is_hit), mf = __ballot_sync(FULL, is_free);
+      unsigned bh = 0, bf = 0;
+      if (lane == 0) { if (mh) bh = atomicAdd(&s_nhit, __popc(mh)); if (mf) bf = atomicAdd(&s_nfree, __popc(mf)); }
+      bh = __shfl_sync(FULL, bh, 0); bf = __shfl_sync(FULL, bf, 0);
+      const unsigned below = (1u << lane) - 1;
+      if (is_hit) s_hit[bh + __popc(mh & below)] = (unsigned short)j;
+      if (is_free) s_free[bf + __popc(mf & below)] = (unsigned short)j;
+    }
+    __syncthreads();
+    // ---- pass 1: shade the hits
+    const unsigned n_hit = s_nhit;
+    for (unsigned t = threadIdx.x; t < n_hit; t += 256) {
+      const int j = s_hit[t], k = base + j;
+      const float4 t4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
+      const int2 h = pool.hit[k];
+      const uint2 id = pool.id[k];
+      int bounce = __float_as_int(t4.w);
+      Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
+      V3 thr = mk(t4.x, t4.y, t4.z), L = mk(l4.x, l4.y, l4.z);
+      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
+      if (done) {
+        float* px = accum + (size_t)id.x * 3;
+        atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
+        s_free[atomicAdd(&s_nfree, 1u)] = (unsigned short)j;
+      } else {
+        pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+        pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+        pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
+        pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
+        ++n_seg;
+      }
+    }
+    __syncthreads();
+    // ---- pass 2: regenerate
+    const unsigned n_free = s_nfree;
+    if (threadIdx.x == 0) s_base = n_free ? atomicAdd(&cur->path, (unsigned long long)n_free) : total;
+    __syncthreads();
+    const unsigned long long pbase = s_base;
+    for (unsigned t = threadIdx.x; t < n_free; t += 256) {
+      const int k = base + s_free[t];
+      const unsigned long long mine = pbase + t;
+      bool made = false;
+      if (mine < total) {
+        const unsigned q = (unsigned)(mine % per_sample);
+        const int s_off = (int)(mine / per_sample);
+        const int tile = (int)(q >> 5), l = (int)(q & 31);
+        const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
+        if (x < A.W && y < A.H) {
+          const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
+          const Ray r = generate_ray(A, x, y, pixel, sample);
+          pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+          pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+          pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
+          pool.rad[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+          pool.id[k] = make_uint2(pixel, sample);
+          made = true; ++n_new; ++n_seg;
+        }
+      }
+      if (!made) {                                  // no path: extend skips the slot, the next shade pass retries
+        pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
+        pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+      }
+    }
+    __syncthreads();                                // the lists are reused by the next chunk
+  }
+  unsigned long long v0 = n_new, v1 = n_seg, v2 = cnt.tri_hits;
+  for (int o = 16; o > 0; o >>= 1) {
+    v0 += __shfl_down_sync(FULL, v0, o); v1 += __shfl_down_sync(FULL, v1, o);
+    if (COUNT) v2 += __shfl_down_sync(FULL, v2, o);
+  }
+  if (lane == 0) { atomicAdd(&s_stat[0], v0); atomicAdd(&s_stat[1], v1); if (COUNT) atomicAdd(&s_stat[2], v2); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
+    if (s_stat[1]) { atomicAdd(&counters[1], s_stat[1]); cur->alive = 1; }
     if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
   }
 }
