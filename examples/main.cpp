@@ -6,9 +6,13 @@
 // (writeColorTarget + stbi_write_png) becomes the device's resolve + srt_png_write.
 //
 //   g++ -std=c++17 -Iinclude examples/main.cpp -Lsexy-raytracer_b200 -lsrt_host -o sexy-raytracer
-//   SRT_B200_LIBRARY=sexy-raytracer_b200/libsrt_b200.so ./sexy-raytracer [data dir | shirley] [height] [samples] [out.png]
+//   SRT_B200_LIBRARY=sexy-raytracer_b200/libsrt_b200.so ./sexy-raytracer [data dir | shirley] [height] [samples] [out.png] [passes]
+// passes > 1 renders progressively (the reference's `while (glDevice.rtFrame(...))` loop, main.cpp:195-199): samples/passes
+// more samples per pixel per pass into a film on the device, a checkpoint <out.png>.srtf after every pass; an existing
+// checkpoint of the same size is resumed.
 // "shirley" renders the sphere scene of the commented block main.cpp:92-122 (needs no asset files) with the camera of
 // the commented line main.cpp:160 and depth 10 (BASELINE config 1).
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <iostream>
@@ -54,9 +58,25 @@ int main(int argc, char** argv) {
     return 1;
   }
   srt_stats stats;
-  if (!device.rtFrame(target, imageWidth, imageHeight, mainCamera, background, numSamples, maxBounce, 1, &stats)) {   // main.cpp:197-227
-    std::cerr << "device: " << device.lastError() << "\n";
-    return 1;
+  const int passes = argc > 5 ? atoi(argv[5]) : 1;
+  if (passes <= 1) {
+    if (!device.rtFrame(target, imageWidth, imageHeight, mainCamera, background, numSamples, maxBounce, 1, &stats)) {   // main.cpp:197-227
+      std::cerr << "device: " << device.lastError() << "\n";
+      return 1;
+    }
+  } else {
+    const std::string ckpt = std::string(outFile) + ".srtf";
+    if (device.loadCheckpoint(ckpt.c_str(), imageWidth, imageHeight))
+      std::cerr << "resuming " << ckpt << " at " << device.samplesDone() << " samples per pixel\n";
+    while (device.samplesDone() < numSamples) {                 // while (glDevice.rtFrame(...))  main.cpp:195-199
+      const int k = std::min((numSamples + passes - 1) / passes, numSamples - device.samplesDone());
+      if (!device.rtFrameProgressive(target, imageWidth, imageHeight, mainCamera, background, k, maxBounce, 1, &stats) ||
+          !device.saveCheckpoint(ckpt.c_str())) {
+        std::cerr << "device: " << device.lastError() << "\n";
+        return 1;
+      }
+      std::cerr << "\r" << device.samplesDone() << " / " << numSamples << " samples per pixel " << std::flush;
+    }
   }
   device.terminate();                                           // main.cpp:231
 

@@ -215,6 +215,21 @@ srt_status  srt_render_accumulate(srt_scene* scene, const srt_camera* cam, const
 srt_status  srt_resolve(srt_device* dev, const float* sum_dev, int32_t width, int32_t height, int32_t spp,
                         uint8_t* rgba8_dev);
 
+/* ---- progressive accumulation: glDevice::rtFrame as a per-frame loop (main.cpp:195-199, gl.h:269-320), headless ----
+ * A film is a persistent fp32 sum buffer on the device + the number of samples per pixel it holds.  add_samples
+ * renders the next `count` GLOBAL sample indices of every pixel into it (params->spp / sample_begin / sample_count are
+ * ignored): the Philox stream is keyed by the global index, so K calls of n samples give the frame of one call of
+ * K*n samples up to fp32 summation order.  resolve applies writeColorTarget (color.h:25-41) with the samples so far;
+ * load restores a saved sum buffer (checkpoint / resume, see srt_checkpoint_* in srt_host.h).                     */
+typedef struct srt_film srt_film;
+srt_status  srt_film_create(srt_device* dev, int32_t width, int32_t height, srt_film** out);
+void        srt_film_destroy(srt_film* film);
+srt_status  srt_film_add_samples(srt_film* film, srt_scene* scene, const srt_camera* cam, const srt_render_params* params,
+                                 int32_t count, srt_stats* stats);
+int32_t     srt_film_samples(const srt_film* film);
+srt_status  srt_film_resolve(srt_film* film, uint8_t* out_rgba8 /*optional, W*H*4*/, float* out_sum_rgb /*optional, W*H*3*/);
+srt_status  srt_film_load(srt_film* film, const float* sum_rgb /*W*H*3*/, int32_t samples_done);
+
 /* ---- per-function known-answer entry points (random numbers injected) ------------------------ */
 /* material::scatter + emitted for n (ray, hit) pairs; xi[n*4] are the uniform [0,1) numbers the
  * sampler consumes ("random numbers").  out_scattered[i] = 0/1 return of scatter. */

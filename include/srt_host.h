@@ -55,6 +55,14 @@ srt_status srt_png_read_memory(const uint8_t* file_bytes, int64_t len, int32_t r
 srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, const uint8_t* pixels, int32_t stride_bytes);
 void       srt_host_free(void* p);
 
+/* ---- checkpoint of a progressive render: the fp32 sum buffer + how many samples per pixel it holds.
+ * File: "SRTF" u32 version=1, i32 width, height, samples_done, u64 seed, then width*height*3 little-endian floats.   */
+srt_status srt_checkpoint_write(const char* path, int32_t width, int32_t height, int32_t samples_done, uint64_t seed,
+                                const float* sum_rgb);
+/* *out_sum_rgb is malloc'ed (free with srt_host_free) */
+srt_status srt_checkpoint_read(const char* path, int32_t* width, int32_t* height, int32_t* samples_done, uint64_t* seed,
+                               float** out_sum_rgb);
+
 /* ---- whole scenes through the C++ host classes of srt_world.hpp (for callers that are not C++: tests, bench) ----------
  * which: 1 = the Shirley sphere block of main.cpp:92-122 re-enabled (+ main.cpp:124-131,143-144)   [BASELINE config 1]
  *        2 = cube.gltf + square.gltf + ground + light                                              [BASELINE config 2]

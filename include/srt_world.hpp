@@ -293,12 +293,23 @@ class b200Device {
   bool init(int w, int h, const hittableList& world, int gpu = 0, const char* library_path = nullptr);
   bool rtFrame(void* frameData, int w, int h, const camera& cam, const color3f& background, int numSamples, int maxBounce,
                uint64_t seed = 1, srt_stats* stats = nullptr);
+  // Progressive form - what the reference's `while (glDevice.rtFrame(...))` loop is for (main.cpp:195-199): each call adds
+  // `samples` more samples per pixel to a film that stays on the device and resolves the frame so far into frameData.
+  // saveCheckpoint / loadCheckpoint write / restore the film (fp32 sums + sample count) so a long render can resume.
+  bool rtFrameProgressive(void* frameData, int w, int h, const camera& cam, const color3f& background, int samples, int maxBounce,
+                          uint64_t seed = 1, srt_stats* stats = nullptr);
+  int  samplesDone() const;
+  bool saveCheckpoint(const char* path);
+  bool loadCheckpoint(const char* path, int w, int h);
   void terminate();
   const std::string& lastError() const { return err; }
  private:
   void* so = nullptr;
   srt_device* dev = nullptr;
   srt_scene* scene = nullptr;
+  srt_film* film = nullptr;
+  int film_w = 0, film_h = 0;
+  uint64_t film_seed = 1;
   std::string err;
 };
 

@@ -94,6 +94,12 @@ PROTOTYPES = {
     "srt_render": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.POINTER(Stats)]),
     "srt_render_accumulate": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, C.POINTER(Stats)]),
     "srt_resolve": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_int32, _vp]),
+    "srt_film_create": (C.c_int, [_vp, C.c_int32, C.c_int32, C.POINTER(_vp)]),
+    "srt_film_destroy": (None, [_vp]),
+    "srt_film_add_samples": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(RenderParams), C.c_int32, C.POINTER(Stats)]),
+    "srt_film_samples": (C.c_int32, [_vp]),
+    "srt_film_resolve": (C.c_int, [_vp, _vp, _vp]),
+    "srt_film_load": (C.c_int, [_vp, _vp, C.c_int32]),
     "srt_shade_kat": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp]),
     "srt_texture_kat": (C.c_int, [_vp, C.c_int32, _vp, C.c_int64, _vp]),
     "srt_getray_kat": (C.c_int, [_vp, C.POINTER(Camera), _vp, C.c_int64, _vp]),

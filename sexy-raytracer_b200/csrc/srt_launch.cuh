@@ -412,3 +412,84 @@ srt_status srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_re
 }
 
 }  // extern "C"
+
+// ---- progressive accumulation: the role of glDevice::rtFrame as a per-frame loop (main.cpp:195-199, gl.h:269-320), headless ----
+struct srt_film {
+  srt_device* dev = nullptr;
+  int W = 0, H = 0;
+  int done = 0;                 // samples per pixel accumulated so far = the next global sample index
+  float* sum = nullptr;         // device, [H*W*3]
+};
+
+extern "C" {
+
+srt_status srt_film_create(srt_device* dev, int32_t W, int32_t H, srt_film** out) {
+  if (!dev || !out || W <= 0 || H <= 0) return fail(SRT_ERR_INVALID, "bad argument");
+  *out = nullptr;
+  CK(cudaSetDevice(dev->gpu));
+  srt_film* f = new srt_film;
+  f->dev = dev; f->W = W; f->H = H;
+  const size_t nb = (size_t)W * H * 3 * sizeof(float);
+  cudaError_t e = cudaMalloc(&f->sum, nb);
+  if (e != cudaSuccess) { cudaGetLastError(); delete f; return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
+  e = cudaMemsetAsync(f->sum, 0, nb, dev->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(dev->stream);
+  if (e != cudaSuccess) { cudaGetLastError(); cudaFree(f->sum); delete f; return fail(SRT_ERR_CUDA, cudaGetErrorString(e)); }
+  *out = f;
+  return SRT_OK;
+}
+
+void srt_film_destroy(srt_film* f) {
+  if (!f) return;
+  cudaSetDevice(f->dev->gpu);
+  if (f->sum) cudaFree(f->sum);
+  delete f;
+}
+
+int32_t srt_film_samples(const srt_film* f) { return f ? f->done : 0; }
+
+srt_status srt_film_add_samples(srt_film* f, srt_scene* s, const srt_camera* cam, const srt_render_params* P, int32_t count,
+                                srt_stats* stats) {
+  if (!f || !s || !P || count <= 0) return fail(SRT_ERR_INVALID, "bad argument");
+  if (s->dev != f->dev) return fail(SRT_ERR_INVALID, "film and scene live on different devices");
+  if (P->width != f->W || P->height != f->H) return fail(SRT_ERR_INVALID, "render size differs from the film's");
+  srt_render_params q = *P;
+  q.sample_begin = f->done; q.sample_count = count;
+  q.spp = f->done + count;                      // only resolve divides by spp; the sample range is what the kernels use
+  srt_status rc = srt_render_accumulate(s, cam, &q, f->sum, stats);
+  if (rc) return rc;
+  f->done += count;
+  return SRT_OK;
+}
+
+srt_status srt_film_resolve(srt_film* f, uint8_t* out_rgba8, float* out_sum_rgb) {
+  if (!f) return fail(SRT_ERR_INVALID, "film is NULL");
+  if (f->done <= 0) return fail(SRT_ERR_INVALID, "no samples accumulated yet");
+  srt_device* dev = f->dev;
+  CK(cudaSetDevice(dev->gpu));
+  const size_t n = (size_t)f->W * f->H;
+  if (out_rgba8) {
+    DevBuf rgba;
+    CK(rgba.alloc(n * 4));
+    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, dev->stream>>>(f->sum, (int)n, f->done, rgba.as<uchar4>());
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_rgba8, rgba.p, n * 4, cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));
+  }
+  if (out_sum_rgb) {
+    CK(cudaMemcpyAsync(out_sum_rgb, f->sum, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaStreamSynchronize(dev->stream));
+  }
+  return SRT_OK;
+}
+
+srt_status srt_film_load(srt_film* f, const float* sum_rgb, int32_t samples_done) {
+  if (!f || !sum_rgb || samples_done < 0) return fail(SRT_ERR_INVALID, "bad argument");
+  CK(cudaSetDevice(f->dev->gpu));
+  CK(cudaMemcpyAsync(f->sum, sum_rgb, (size_t)f->W * f->H * 3 * sizeof(float), cudaMemcpyHostToDevice, f->dev->stream));
+  CK(cudaStreamSynchronize(f->dev->stream));
+  f->done = samples_done;
+  return SRT_OK;
+}
+
+}  // extern "C"

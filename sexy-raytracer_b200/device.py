@@ -147,3 +147,39 @@ class DeviceScene:
         out = np.zeros((len(uvp), 3), np.float32)
         _check(lib().srt_texture_kat(self.h, tex, _ptr(uvp), len(uvp), _ptr(out)))
         return out
+
+
+class Film:
+    """srt_film: progressive accumulation (the per-frame loop of glDevice::rtFrame, main.cpp:195-199, headless)."""
+
+    def __init__(self, device, width, height):
+        self.device, self.width, self.height = device, width, height
+        self.h = C.c_void_p()
+        _check(lib().srt_film_create(device.h, width, height, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().srt_film_destroy(self.h)
+            self.h = C.c_void_p()
+
+    @property
+    def samples(self):
+        return int(lib().srt_film_samples(self.h))
+
+    def add_samples(self, dscene, count, params=None, camera=None):
+        P = params if params is not None else dscene.scene.render_params(width=self.width, height=self.height)
+        cam = camera if camera is not None else dscene.scene.camera_struct()
+        st = abi.Stats()
+        _check(lib().srt_film_add_samples(self.h, dscene.h, C.byref(cam), C.byref(P), count, C.byref(st)))
+        return st
+
+    def resolve(self, want_sum=True, want_rgba=True):
+        acc = np.zeros((self.height, self.width, 3), np.float32) if want_sum else None
+        rgba = np.zeros((self.height, self.width, 4), np.uint8) if want_rgba else None
+        _check(lib().srt_film_resolve(self.h, _ptr(rgba) if want_rgba else None, _ptr(acc) if want_sum else None))
+        return acc, rgba
+
+    def load(self, sum_rgb, samples_done):
+        a = np.ascontiguousarray(sum_rgb, np.float32)
+        assert a.size == self.width * self.height * 3
+        _check(lib().srt_film_load(self.h, _ptr(a), samples_done))

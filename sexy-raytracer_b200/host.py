@@ -81,6 +81,9 @@ def _bind_world(L):
                                       C.POINTER(C.POINTER(C.c_uint8))]
     L.srt_png_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32]
     L.srt_host_free.argtypes = [C.c_void_p]
+    L.srt_checkpoint_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_uint64, C.c_void_p]
+    L.srt_checkpoint_read.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
+                                      C.POINTER(C.POINTER(C.c_float))]
     L.srt_bvh_build_ordered.argtypes = [C.POINTER(abi.SceneDesc), C.c_void_p, C.c_float, C.c_float, C.c_uint64, C.c_int,
                                         C.POINTER(C.POINTER(abi.BvhNode)), C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]
     L._world_bound = True
@@ -172,3 +175,19 @@ def png_write(path, pixels):
     if a.ndim == 2:
         a = a[:, :, None]
     _check(L.srt_png_write(os.fsencode(path), a.shape[1], a.shape[0], a.shape[2], a.ctypes.data_as(C.c_void_p), 0))
+
+
+def checkpoint_write(path, sum_rgb, samples_done, seed=1):
+    """srt_checkpoint_write: the film of a progressive render (fp32 sums [h, w, 3] + samples per pixel so far)."""
+    a = np.ascontiguousarray(sum_rgb, np.float32)
+    _check(_bind_world(lib()).srt_checkpoint_write(os.fsencode(path), a.shape[1], a.shape[0], samples_done, seed, a.ctypes.data_as(C.c_void_p)))
+
+
+def checkpoint_read(path):
+    """-> (sum [h, w, 3] f32, samples_done, seed)"""
+    L = _bind_world(lib())
+    w, h, n, seed, p = C.c_int32(), C.c_int32(), C.c_int32(), C.c_uint64(), C.POINTER(C.c_float)()
+    _check(L.srt_checkpoint_read(os.fsencode(path), C.byref(w), C.byref(h), C.byref(n), C.byref(seed), C.byref(p)))
+    a = np.ctypeslib.as_array(p, shape=(h.value * w.value * 3,)).copy().reshape(h.value, w.value, 3)
+    L.srt_host_free(p)
+    return a, n.value, seed.value

@@ -237,4 +237,36 @@ srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, c
   return ok ? SRT_OK : fail(SRT_ERR_INVALID, std::string("write error on ") + path);
 }
 
+
+srt_status srt_checkpoint_write(const char* path, int32_t w, int32_t h, int32_t samples_done, uint64_t seed, const float* sum) {
+  if (!path || !sum || w <= 0 || h <= 0 || samples_done < 0) return fail(SRT_ERR_INVALID, "bad argument");
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(SRT_ERR_INVALID, std::string("cannot create ") + path);
+  const uint32_t ver = 1;
+  const size_t n = (size_t)w * h * 3;
+  bool ok = fwrite("SRTF", 1, 4, f) == 4 && fwrite(&ver, 4, 1, f) == 1 && fwrite(&w, 4, 1, f) == 1 && fwrite(&h, 4, 1, f) == 1 &&
+            fwrite(&samples_done, 4, 1, f) == 1 && fwrite(&seed, 8, 1, f) == 1 && fwrite(sum, sizeof(float), n, f) == n;
+  ok = (fclose(f) == 0) && ok;
+  return ok ? SRT_OK : fail(SRT_ERR_INVALID, std::string("write error on ") + path);
+}
+
+srt_status srt_checkpoint_read(const char* path, int32_t* w, int32_t* h, int32_t* samples_done, uint64_t* seed, float** out) {
+  if (!path || !w || !h || !samples_done || !seed || !out) return fail(SRT_ERR_INVALID, "NULL argument");
+  *out = nullptr;
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(SRT_ERR_INVALID, std::string("cannot open ") + path);
+  char magic[4]; uint32_t ver = 0;
+  bool ok = fread(magic, 1, 4, f) == 4 && !memcmp(magic, "SRTF", 4) && fread(&ver, 4, 1, f) == 1 && ver == 1 && fread(w, 4, 1, f) == 1 &&
+            fread(h, 4, 1, f) == 1 && fread(samples_done, 4, 1, f) == 1 && fread(seed, 8, 1, f) == 1;
+  if (!ok || *w <= 0 || *h <= 0 || *samples_done < 0 || (int64_t)*w * *h > (1ll << 32)) { fclose(f); return fail(SRT_ERR_INVALID, "not a checkpoint file"); }
+  const size_t n = (size_t)*w * *h * 3;
+  float* p = (float*)malloc(n * sizeof(float));
+  if (!p) { fclose(f); return fail(SRT_ERR_NOMEM, "checkpoint buffer"); }
+  const bool full = fread(p, sizeof(float), n, f) == n;
+  fclose(f);
+  if (!full) { free(p); return fail(SRT_ERR_INVALID, "truncated checkpoint file"); }
+  *out = p;
+  return SRT_OK;
+}
+
 }  // extern "C"

@@ -566,6 +566,12 @@ struct Api {
   void (*scene_destroy)(srt_scene*);
   srt_status (*render)(srt_scene*, const srt_camera*, const srt_render_params*, float*, uint8_t*, srt_stats*);
   const char* (*last_error)(void);
+  srt_status (*film_create)(srt_device*, int32_t, int32_t, srt_film**);
+  void (*film_destroy)(srt_film*);
+  srt_status (*film_add)(srt_film*, srt_scene*, const srt_camera*, const srt_render_params*, int32_t, srt_stats*);
+  int32_t (*film_samples)(const srt_film*);
+  srt_status (*film_resolve)(srt_film*, uint8_t*, float*);
+  srt_status (*film_load)(srt_film*, const float*, int32_t);
 };
 bool bind(void* so, Api& a) {
   a.device_create = (decltype(a.device_create))dlsym(so, "srt_device_create");
@@ -574,7 +580,14 @@ bool bind(void* so, Api& a) {
   a.scene_destroy = (decltype(a.scene_destroy))dlsym(so, "srt_scene_destroy");
   a.render = (decltype(a.render))dlsym(so, "srt_render");
   a.last_error = (decltype(a.last_error))dlsym(so, "srt_last_error");
-  return a.device_create && a.device_destroy && a.scene_create && a.scene_destroy && a.render && a.last_error;
+  a.film_create = (decltype(a.film_create))dlsym(so, "srt_film_create");
+  a.film_destroy = (decltype(a.film_destroy))dlsym(so, "srt_film_destroy");
+  a.film_add = (decltype(a.film_add))dlsym(so, "srt_film_add_samples");
+  a.film_samples = (decltype(a.film_samples))dlsym(so, "srt_film_samples");
+  a.film_resolve = (decltype(a.film_resolve))dlsym(so, "srt_film_resolve");
+  a.film_load = (decltype(a.film_load))dlsym(so, "srt_film_load");
+  return a.device_create && a.device_destroy && a.scene_create && a.scene_destroy && a.render && a.last_error && a.film_create &&
+         a.film_destroy && a.film_add && a.film_samples && a.film_resolve && a.film_load;
 }
 }  // namespace
 
@@ -607,16 +620,74 @@ bool b200Device::rtFrame(void* frameData, int w, int h, const camera& cam, const
   return true;
 }
 
+bool b200Device::rtFrameProgressive(void* frameData, int w, int h, const camera& cam, const color3f& background, int samples,
+                                    int maxBounce, uint64_t seed, srt_stats* stats) {
+  if (!scene) { err = "rtFrameProgressive before init"; return false; }
+  Api a;
+  bind(so, a);
+  if (film && (film_w != w || film_h != h)) { a.film_destroy(film); film = nullptr; }
+  if (!film) {
+    if (a.film_create(dev, w, h, &film) != SRT_OK) { err = a.last_error(); film = nullptr; return false; }
+    film_w = w; film_h = h;
+  }
+  film_seed = seed;
+  srt_render_params p;
+  memset(&p, 0, sizeof p);
+  p.width = w; p.height = h; p.max_bounce = maxBounce; p.seed = seed;
+  for (int k = 0; k < 3; k++) p.background[k] = background(k);
+  srt_stats st;
+  if (a.film_add(film, scene, &cam.desc(), &p, samples, &st) != SRT_OK) { err = a.last_error(); return false; }
+  if (stats) *stats = st;
+  if (frameData && a.film_resolve(film, static_cast<uint8_t*>(frameData), nullptr) != SRT_OK) { err = a.last_error(); return false; }
+  return true;
+}
+
+int b200Device::samplesDone() const {
+  if (!film) return 0;
+  Api a;
+  bind(so, a);
+  return a.film_samples(film);
+}
+
+bool b200Device::saveCheckpoint(const char* path) {
+  if (!film) { err = "no progressive render to save"; return false; }
+  Api a;
+  bind(so, a);
+  std::vector<float> sum((size_t)film_w * film_h * 3);
+  if (a.film_resolve(film, nullptr, sum.data()) != SRT_OK) { err = a.last_error(); return false; }
+  if (srt_checkpoint_write(path, film_w, film_h, a.film_samples(film), film_seed, sum.data()) != SRT_OK) { err = srt_host_last_error(); return false; }
+  return true;
+}
+
+bool b200Device::loadCheckpoint(const char* path, int w, int h) {
+  if (!scene) { err = "loadCheckpoint before init"; return false; }
+  Api a;
+  bind(so, a);
+  int32_t cw = 0, ch = 0, done = 0;
+  uint64_t seed = 0;
+  float* sum = nullptr;
+  if (srt_checkpoint_read(path, &cw, &ch, &done, &seed, &sum) != SRT_OK) { err = srt_host_last_error(); return false; }
+  if (cw != w || ch != h) { srt_host_free(sum); err = "checkpoint is of a different frame size"; return false; }
+  if (film && (film_w != w || film_h != h)) { a.film_destroy(film); film = nullptr; }
+  if (!film && a.film_create(dev, w, h, &film) != SRT_OK) { srt_host_free(sum); err = a.last_error(); film = nullptr; return false; }
+  film_w = w; film_h = h; film_seed = seed;
+  const srt_status rc = a.film_load(film, sum, done);
+  srt_host_free(sum);
+  if (rc != SRT_OK) { err = a.last_error(); return false; }
+  return true;
+}
+
 void b200Device::terminate() {
   if (so) {
     Api a;
     if (bind(so, a)) {
+      if (film) a.film_destroy(film);
       if (scene) a.scene_destroy(scene);
       if (dev) a.device_destroy(dev);
     }
     dlclose(so);
   }
-  so = nullptr; dev = nullptr; scene = nullptr;
+  so = nullptr; dev = nullptr; scene = nullptr; film = nullptr;
 }
 
 }  // namespace srt

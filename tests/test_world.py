@@ -287,3 +287,72 @@ def test_example_renders_config1_like_the_library(tmp_path, device, dev_scenes, 
     assert (got[..., 3] == 255).all()
     # the same kernels on the same description and seed: identical up to the order of the atomic adds of the accumulation
     assert (np.abs(got.astype(int) - want.astype(int)) <= 1).mean() > 0.999
+
+
+# ---- progressive accumulation + checkpoint ----------------------------------------------------------
+def test_checkpoint_round_trip(tmp_path):
+    rng = np.random.default_rng(3)
+    a = rng.random((7, 11, 3), dtype=np.float32) * 100
+    p = str(tmp_path / "film.srtf")
+    host.checkpoint_write(p, a, 123, seed=0xDEADBEEF12345)
+    b, n, seed = host.checkpoint_read(p)
+    assert n == 123 and seed == 0xDEADBEEF12345 and b.tobytes() == a.tobytes()
+    (tmp_path / "short.srtf").write_bytes(open(p, "rb").read()[:-8])
+    with pytest.raises(RuntimeError):
+        host.checkpoint_read(str(tmp_path / "short.srtf"))
+    (tmp_path / "junk.srtf").write_bytes(b"PNG?" * 20)
+    with pytest.raises(RuntimeError):
+        host.checkpoint_read(str(tmp_path / "junk.srtf"))
+
+
+@pytest.mark.gpu
+def test_film_progressive_equals_one_call(device, dev_scenes, scenes, tmp_path):
+    """K calls of n samples = one call of K*n samples (Philox is keyed by the global sample index), also across a
+    checkpoint written by srt_checkpoint_write and restored into a new film."""
+    from sexy_raytracer_b200.device import Film
+    s, ds = scenes["c3_masterchief"], dev_scenes["c3_masterchief"]
+    W, H = 160, 90
+    want, want_rgba, st = ds.render(s.render_params(width=W, height=H, spp=16, seed=5))
+    P = s.render_params(width=W, height=H, seed=5)
+    film = Film(device, W, H)
+    segs = 0
+    for _ in range(2):
+        segs += int(film.add_samples(ds, 4, P).segments)
+    assert film.samples == 8
+    half, _ = film.resolve(want_rgba=False)
+    host.checkpoint_write(str(tmp_path / "f.srtf"), half, film.samples, seed=5)
+    film.close()
+    saved, done, seed = host.checkpoint_read(str(tmp_path / "f.srtf"))
+    film2 = Film(device, W, H)
+    film2.load(saved, done)
+    for _ in range(2):
+        segs += int(film2.add_samples(ds, 4, P).segments)
+    assert film2.samples == 16 and segs == int(st.segments)
+    got, got_rgba = film2.resolve()
+    film2.close()
+    fin = np.isfinite(want).all(axis=2)
+    assert (np.isfinite(got).all(axis=2) == fin).all()
+    assert np.abs(got[fin] - want[fin]).max() <= 2e-5 * max(1.0, np.abs(want[fin]).max())
+    assert (np.abs(got_rgba.astype(int) - want_rgba.astype(int)) <= 1).all()
+    with pytest.raises(Exception):
+        Film(device, 0, 10)
+
+
+@pytest.mark.gpu
+def test_example_progressive_resumes(tmp_path):
+    """examples/sexy-raytracer with passes: 16 samples in 4 passes, killed-and-resumed from the checkpoint = one 16-sample run."""
+    from sexy_raytracer_b200 import build
+    exe = build.build_example()
+    env = dict(os.environ, SRT_B200_LIBRARY=build.LIB)
+    one = str(tmp_path / "one.png")
+    assert subprocess.run([exe, "shirley", "90", "16", one], capture_output=True, env=env).returncode == 0
+    prog = str(tmp_path / "prog.png")
+    assert subprocess.run([exe, "shirley", "90", "8", prog, "2"], capture_output=True, env=env).returncode == 0     # stops at 8
+    _, done, _ = host.checkpoint_read(prog + ".srtf")
+    assert done == 8
+    r = subprocess.run([exe, "shirley", "90", "16", prog, "4"], capture_output=True, text=True, env=env)              # resumes to 16
+    assert r.returncode == 0 and "resuming" in r.stderr
+    _, done, _ = host.checkpoint_read(prog + ".srtf")
+    assert done == 16
+    a, b = host.png_read(one, 4), host.png_read(prog, 4)
+    assert a.shape == b.shape and (np.abs(a.astype(int) - b.astype(int)) <= 1).mean() > 0.999
