@@ -270,7 +270,9 @@ def run_b200(args):
     e2e_seg = 0
     barrier()
     t0 = time.perf_counter()
+    e2e_steps = []
     for _ in range(args.steps):
+        t_step = time.perf_counter()
         ds2 = dev.upload(scene)                                        # H2D: the flattened scene, every step
         if world == 1:
             _, frame, st = ds2.render(P, want_sum=False, want_rgba=True)   # D2H: the RGBA8 frame
@@ -285,6 +287,7 @@ def run_b200(args):
             dev.set_stream(None)
         e2e_seg += int(st.segments) if st is not None else 0
         ds2.close()
+        e2e_steps.append(round(time.perf_counter() - t_step, 4))
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -368,7 +371,7 @@ def run_b200(args):
                 "segments_per_step": seg_all / args.steps, "paths_per_step": paths_all / args.steps,
                 "render_kernel_ms_per_step": round(kern_ms_max / args.steps, 3),
                 "e2e": {"value": round(e2e_value, 2), "unit": "M segments/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "s_per_step": round(te.item() / args.steps, 4),
+                        "s_per_step": round(te.item() / args.steps, 4), "s_steps_rank0": e2e_steps,
                         "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out)" if world == 1 else
                                 "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H"},
                 "gpu_launches": launches, "variant": variant, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}

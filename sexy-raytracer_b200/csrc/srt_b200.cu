@@ -1,6 +1,7 @@
 // srt_b200.cu — host side of the C ABI (include/srt.h) + kernel launches.  Built into libsrt_b200.so:
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false ...   (see build.py)
 // No torch types, no CPU fallback: every compute entry point needs a CUDA device.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>

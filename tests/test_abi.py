@@ -16,8 +16,8 @@ def lib():
     return C.CDLL(build.LIB)
 
 
-def declared_symbols():
-    src = open(os.path.join(ROOT, "include", "srt.h")).read()
+def declared_symbols(header="srt.h"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(srt_[a-z_0-9]+)\s*\(", src)))
 
@@ -29,6 +29,18 @@ def test_abi_symbols(lib):
         assert hasattr(lib, n), "libsrt_b200.so does not export %s" % n
     lib.srt_abi_version.restype = C.c_int
     assert lib.srt_abi_version() == 1
+
+
+def test_host_abi_symbols():
+    """libsrt_host.so (plain C++, no CUDA) exports every symbol include/srt_host.h declares, and the C++ classes of
+    include/srt_world.hpp link against it (examples/main.cpp is the link test)."""
+    build.build_host()
+    L = C.CDLL(build.HOST_LIB)
+    names = declared_symbols("srt_host.h")
+    assert len(names) >= 15 and "srt_bvh_build" in names and "srt_png_write" in names and "srt_checkpoint_read" in names
+    for n in names:
+        assert hasattr(L, n), "libsrt_host.so does not export %s" % n
+    assert os.access(build.build_example(), os.X_OK)
 
 
 def test_struct_sizes_match_header():
