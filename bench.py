@@ -353,6 +353,13 @@ def run_b200(args):
                     "fp32": {"achieved_tflops": round(fl, 3), "peak_nominal_tflops": round(fp32_peak, 1),
                              "frac_fma_peak": round(fl / fp32_peak, 4), "frac_unfused_peak": round(fl / (fp32_peak / 2), 4),
                              "flops_per_segment": round(fl_seg, 1)}}
+        try:   # the un-fused mul + add ceiling measured on this pool's B200 (tools/fp32_peak.cu)
+            mp = json.load(open(os.path.join(ROOT, "profiles", "r1_fp32_peak_b200.json")))
+            roofline["fp32"]["peak_measured_unfused_tflops"] = mp["unfused_mul_add_tflops"]
+            roofline["fp32"]["peak_measured_ffma_tflops"] = mp["ffma_tflops"]
+            roofline["fp32"]["frac_measured_unfused_peak"] = round(fl / mp["unfused_mul_add_tflops"], 4)
+        except (OSError, ValueError, KeyError):
+            pass
         cpu = None
         if world == 1 and not args.no_cpu:
             v, desc = cpu_frame_sample(args, scene=scene)

@@ -168,6 +168,10 @@ typedef struct srt_render_params {
   int32_t  rr_begin;       /* Russian roulette from this bounce on; 0 = off (the reference has none) */
   int32_t  variant;        /* 0 = auto (wavefront for frames of >= 4 Mi paths over trees of >= 256 nodes, else megakernel),
                               1 = flat megakernel, 2 = wavefront, 3 = phased megakernel         */
+  int32_t  sampler;        /* where in the pixel a sample lies: 0 = random jitter (main.cpp:210-211, the live code),
+                              1 = the 4x rotated grid main.cpp:205-207,214-215 keeps commented out: sample s sits at
+                              R_z(15 deg + 90 deg * s) * (0, 0.8) from the pixel's corner (four positions, evaluated
+                              in the reference's fp32 arithmetic); lens, shutter time and scatter draws are unchanged */
 } srt_render_params;
 
 typedef struct srt_stats {

@@ -303,6 +303,9 @@ class b200Device {
   bool loadCheckpoint(const char* path, int w, int h);
   void terminate();
   const std::string& lastError() const { return err; }
+  // where a sample lies inside its pixel: 0 = random jitter (main.cpp:210-211), 1 = the 4x rotated grid the reference keeps
+  // commented out (main.cpp:205-207,214-215); see srt_render_params::sampler
+  int sampler = 0;
  private:
   void* so = nullptr;
   srt_device* dev = nullptr;

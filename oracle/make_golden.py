@@ -61,8 +61,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--no-images", action="store_true")
     ap.add_argument("--aabb-only", action="store_true")
+    ap.add_argument("--sampler-only", action="store_true")
     args = ap.parse_args()
     R = RefOracle()
+    if args.sampler_only:
+        # main.cpp:205-207 as the reference computes it, samples 0..63 (the angle is not reduced mod 360)
+        np.savez_compressed(os.path.join(ROOT, "tests", "golden", "sampler_kat.npz"),
+                            pos=np.stack([R.rotated_grid(s) for s in range(64)]))
+        return
     os.makedirs(os.path.join(ROOT, "scenes"), exist_ok=True)
     gold = os.path.join(ROOT, "tests", "golden")
     os.makedirs(gold, exist_ok=True)

@@ -609,4 +609,15 @@ void ref_aabb_kat(const srt_ray* rays, const float* box, const float* tMinMax, i
   }
 }
 
+// The in-pixel position of sample s under the 4x rotated grid main.cpp keeps commented out: the statements of
+// main.cpp:181,205-207 run as they stand (Eigen's AngleAxisf), out = newSamplePos(0), newSamplePos(1)
+void ref_rotated_grid(int s, float* out) {
+  const vec3f samplePos(0, 0.8f, 0);
+  Eigen::AngleAxisf rotate(deg2rad(15.0f) + deg2rad(90.0f * s), vec3f::UnitZ());
+  Eigen::Matrix<float, 3, 3> m = rotate.matrix();                          // mat33f, main.cpp:26
+  vec3f       newSamplePos = m * samplePos;
+  out[0] = newSamplePos(0);
+  out[1] = newSamplePos(1);
+}
+
 }  // extern "C"

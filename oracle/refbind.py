@@ -183,6 +183,11 @@ class RefOracle:
         self.lib.ref_texture_kat(h, tex, _ptr(uvp), len(uvp), _ptr(out))
         return out
 
+    def rotated_grid(self, s):
+        out = np.zeros(2, np.float32)
+        self.lib.ref_rotated_grid(C.c_int(int(s)), _ptr(out))
+        return out
+
     def aabb_kat(self, rays, boxes, tminmax):
         rays = np.ascontiguousarray(rays, abi.RAY_DTYPE)
         boxes = np.ascontiguousarray(boxes, np.float32).reshape(-1, 6)
@@ -265,6 +270,11 @@ class PortOracle:
         out = np.zeros(len(inp), abi.RAY_DTYPE)
         self.lib.so_getray_kat(C.byref(cam), _ptr(inp), len(inp), _ptr(out))
         return out
+
+    def rotated_grid(self, s):
+        x, y = C.c_float(), C.c_float()
+        self.lib.so_rotated_grid(C.c_int(int(s)), C.byref(x), C.byref(y))
+        return np.array([x.value, y.value], np.float32)
 
     def philox(self, seed, pixel, sample, block):
         out = np.zeros(4, np.uint32)

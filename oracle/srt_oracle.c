@@ -550,6 +550,15 @@ typedef struct {
   const so_scene* s; const srt_camera* cam; const srt_render_params* P; int y0, y1; float* sum; uint64_t paths, segments;
 } band_t;
 
+/* main.cpp:181,205-207 (commented-out 4x rotated grid): AngleAxisf(deg2rad(15) + deg2rad(90 s), UnitZ) * (0, 0.8, 0);
+   Eigen's matrix for the z axis has m01 = -sin(angle), m11 = cos(angle) (Geometry/AngleAxis.h toRotationMatrix) */
+void so_rotated_grid(int s, float* x, float* y) {
+  const float pi = 3.1415926535897932385f;                                                         /* globals.h:15 */
+  float ang = 15.0f * pi / 180.0f + (90.0f * (float)s) * pi / 180.0f;                               /* globals.h:26-28 */
+  *x = -sinf(ang) * 0.8f;
+  *y = cosf(ang) * 0.8f;
+}
+
 /* main.cpp:200-227 over rows [y0, y1) and global samples [sample_begin, sample_begin + sample_count) */
 static void* render_band(void* arg) {
   band_t* b = (band_t*)arg;
@@ -565,8 +574,10 @@ static void* render_band(void* arg) {
         uint32_t a[4], c[4];
         so_philox(P->seed, pixel, sample, 0, a);
         so_philox(P->seed, pixel, sample, 1, c);
-        float u = ((float)x + u01(a[0])) / (float)(W - 1);                                          /* main.cpp:210 */
-        float v = ((float)(H - y) + u01(a[1])) / (float)(H - 1);                                    /* main.cpp:211 */
+        float ju = u01(a[0]), jv = u01(a[1]);
+        if (P->sampler == 1) so_rotated_grid((int)sample, &ju, &jv);                               /* main.cpp:214-215 */
+        float u = ((float)x + ju) / (float)(W - 1);                                                 /* main.cpp:210 */
+        float v = ((float)(H - y) + jv) / (float)(H - 1);                                           /* main.cpp:211 */
         float dx, dy;
         sample_disk(u01(a[2]), u01(a[3]), &dx, &dy);
         ray_t r = camera_get_ray(b->cam, u, v, dx, dy, u01(c[0]));

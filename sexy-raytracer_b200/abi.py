@@ -62,7 +62,7 @@ class Hit(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("sample_begin", C.c_int32),
                 ("sample_count", C.c_int32), ("max_bounce", C.c_int32), ("background", C.c_float * 3),
-                ("seed", C.c_uint64), ("rr_begin", C.c_int32), ("variant", C.c_int32)]
+                ("seed", C.c_uint64), ("rr_begin", C.c_int32), ("variant", C.c_int32), ("sampler", C.c_int32)]
 
 
 class Stats(C.Structure):

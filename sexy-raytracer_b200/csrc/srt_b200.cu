@@ -44,6 +44,7 @@ struct srt_device {
   WfCursors* h_wf_ring = nullptr;             // pinned, WF_RING entries
   cudaEvent_t wf_ev[8] = {};
   cudaEvent_t wf_t[16][3] = {};               // per-wave timing ring: before shade, after shade, after extend
+  float2* d_grid = nullptr; size_t grid_cap = 0;   // srt_render_params::sampler == 1 (srt_launch.cuh: ensure_grid)
 };
 static const int WF_RING = 8;
 static const int WF_TRING = 16;
@@ -101,6 +102,7 @@ void srt_device_destroy(srt_device* d) {
   if (!d) return;
   cudaSetDevice(d->gpu);
   if (d->d_counters) cudaFree(d->d_counters);
+  if (d->d_grid) cudaFree(d->d_grid);
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);

@@ -99,13 +99,28 @@ struct RenderArgs {
   int tiles_x, n_tiles;             // 8x4-pixel tiles
   int chunk, n_chunks;              // samples per work unit
   long long n_units;
+  int sampler;                      // srt_render_params::sampler
+  const float2* grid; int grid_begin;   // sampler 1: in-pixel position of global sample s at grid[s - grid_begin]
 };
+
+// main.cpp:181,205-207: samplePos = (0, 0.8, 0) turned about z by deg2rad(15) + deg2rad(90 s) - Eigen's AngleAxisf matrix
+// has m01 = -sin, m11 = cos for the z axis, and the products with samplePos's zeros are exact.  Evaluated on the host
+// (glibc sinf / cosf, as the reference would) for every sample of the call: the angle is not reduced mod 360, so the
+// four positions drift by a few ulp as s grows, and the table keeps that.
+inline void srt_rotated_grid(int s, float* x, float* y) {
+  const float pi = 3.1415926535897932385f;                                   // globals.h:15
+  const float ang = 15.0f * pi / 180.0f + (90.0f * (float)s) * pi / 180.0f;  // globals.h:26-28
+  *x = -sinf(ang) * 0.8f;
+  *y = cosf(ang) * 0.8f;
+}
 
 // One sample of one pixel: the two ray-generation Philox blocks, main.cpp:210-211, camera.h:40-50
 __device__ __forceinline__ Ray generate_ray(const RenderArgs& A, int x, int y, uint32_t pixel, uint32_t sample) {
   uint4 a = philox(A.seed, pixel, sample, 0), c = philox(A.seed, pixel, sample, 1);
-  float u = ((float)x + u01(a.x)) / (float)(A.W - 1);
-  float v = ((float)(A.H - y) + u01(a.y)) / (float)(A.H - 1);
+  float ju = u01(a.x), jv = u01(a.y);
+  if (A.sampler == 1) { const float2 g = __ldg(A.grid + ((int)sample - A.grid_begin)); ju = g.x; jv = g.y; }   // main.cpp:214-215
+  float u = ((float)x + ju) / (float)(A.W - 1);
+  float v = ((float)(A.H - y) + jv) / (float)(A.H - 1);
   float dx, dy;
   sample_disk(u01(a.z), u01(a.w), dx, dy);
   return camera_get_ray(A.cam, u, v, dx, dy, u01(c.x));

@@ -10,6 +10,23 @@ struct DevBuf {   // scoped device allocation
   template <typename T> T* as() { return static_cast<T*>(p); }
 };
 
+// sampler 1: the table of in-pixel positions of global samples [begin, begin + count) on the device (grow-only buffer)
+static srt_status ensure_grid(srt_device* dev, int begin, int count, RenderArgs& A) {
+  CK(cudaSetDevice(dev->gpu));
+  if ((size_t)count > dev->grid_cap) {
+    if (dev->d_grid) CK(cudaFree(dev->d_grid));
+    dev->d_grid = nullptr; dev->grid_cap = 0;
+    CK(cudaMalloc(&dev->d_grid, (size_t)count * sizeof(float2)));
+    dev->grid_cap = (size_t)count;
+  }
+  std::vector<float2> tab((size_t)count);
+  for (int k = 0; k < count; k++) srt_rotated_grid(begin + k, &tab[k].x, &tab[k].y);
+  CK(cudaMemcpyAsync(dev->d_grid, tab.data(), (size_t)count * sizeof(float2), cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  A.sampler = 1; A.grid = dev->d_grid; A.grid_begin = begin;
+  return SRT_OK;
+}
+
 struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
   int wf_slots, wf_th_walk, wf_shade_chunk; const void* wf_shade;     // variant 2
@@ -40,6 +57,9 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   A.cam = *cam; A.W = P->width; A.H = P->height;
   A.sample_begin = P->sample_begin; A.sample_count = P->sample_count > 0 ? P->sample_count : P->spp;
   A.max_bounce = P->max_bounce; A.rr_begin = P->rr_begin;
+  if (P->sampler != 0 && P->sampler != 1) return fail(SRT_ERR_INVALID, "sampler must be 0 (random jitter) or 1 (4x rotated grid)");
+  A.sampler = P->sampler;
+  if (A.sampler == 1) { srt_status rc = ensure_grid(s->dev, A.sample_begin, A.sample_count, A); if (rc != SRT_OK) return rc; }
   A.bg[0] = P->background[0]; A.bg[1] = P->background[1]; A.bg[2] = P->background[2];
   A.seed = P->seed;
   A.tiles_x = (A.W + 7) / 8;
@@ -400,6 +420,12 @@ srt_status srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_re
   CK(cudaSetDevice(dev->gpu));
   RenderArgs A; memset(&A, 0, sizeof A);
   A.cam = *cam; A.W = P->width; A.H = P->height; A.seed = P->seed;
+  if (P->sampler == 1) {
+    int top = 0;
+    for (int64_t i = 0; i < n; i++) { if (sample[i] < 0) return fail(SRT_ERR_INVALID, "negative sample index"); top = sample[i] > top ? sample[i] : top; }
+    srt_status rc = ensure_grid(dev, 0, top + 1, A);
+    if (rc != SRT_OK) return rc;
+  }
   DevBuf dp, dsm, dout;
   CK(dp.alloc(n * 8)); CK(dsm.alloc(n * 4)); CK(dout.alloc(n * sizeof(srt_ray)));
   CK(cudaMemcpyAsync(dp.p, pixel_xy, n * 8, cudaMemcpyHostToDevice, dev->stream));

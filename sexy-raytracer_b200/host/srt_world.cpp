@@ -612,7 +612,7 @@ bool b200Device::rtFrame(void* frameData, int w, int h, const camera& cam, const
   bind(so, a);
   srt_render_params p;
   memset(&p, 0, sizeof p);
-  p.width = w; p.height = h; p.spp = numSamples; p.max_bounce = maxBounce; p.seed = seed;
+  p.width = w; p.height = h; p.spp = numSamples; p.max_bounce = maxBounce; p.seed = seed; p.sampler = sampler;
   for (int k = 0; k < 3; k++) p.background[k] = background(k);
   srt_stats st;
   if (a.render(scene, &cam.desc(), &p, nullptr, static_cast<uint8_t*>(frameData), &st) != SRT_OK) { err = a.last_error(); return false; }
@@ -633,7 +633,7 @@ bool b200Device::rtFrameProgressive(void* frameData, int w, int h, const camera&
   film_seed = seed;
   srt_render_params p;
   memset(&p, 0, sizeof p);
-  p.width = w; p.height = h; p.max_bounce = maxBounce; p.seed = seed;
+  p.width = w; p.height = h; p.max_bounce = maxBounce; p.seed = seed; p.sampler = sampler;
   for (int k = 0; k < 3; k++) p.background[k] = background(k);
   srt_stats st;
   if (a.film_add(film, scene, &cam.desc(), &p, samples, &st) != SRT_OK) { err = a.last_error(); return false; }

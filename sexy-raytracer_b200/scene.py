@@ -131,7 +131,7 @@ class Scene:
         p = abi.RenderParams()
         p.width, p.height, p.spp, p.max_bounce = (int(x) for x in self.render)
         p.background[:] = [float(x) for x in self.background]
-        p.sample_begin, p.sample_count, p.seed, p.rr_begin, p.variant = 0, 0, 1, 0, 0
+        p.sample_begin, p.sample_count, p.seed, p.rr_begin, p.variant, p.sampler = 0, 0, 1, 0, 0, 0
         for k, v in over.items():
             setattr(p, k, v)
         return p

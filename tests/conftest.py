@@ -35,6 +35,9 @@ def golden():
 
         def aabb(self):
             return np.load(os.path.join(GOLDEN, "aabb_kat.npz"))
+
+        def __call__(self, name):
+            return np.load(os.path.join(GOLDEN, name + "_kat.npz"))
     return G()
 
 

@@ -102,6 +102,33 @@ def test_port_sample_split_additive(port, port_scenes, scenes):
     assert np.abs((a + b) - full).max() <= 1e-5 * np.abs(full).max()
 
 
+def test_port_rotated_grid_vs_golden(port, golden, port_scenes, scenes):
+    """sampler 1: the port's in-pixel positions equal, bit for bit, what the reference's own statements (main.cpp:181,205-207,
+    run through Eigen's AngleAxisf by oracle/ref_oracle.cpp) gave for samples 0..63; the frame it renders is deterministic,
+    differs from the jittered one and splits additively over sample ranges like sampler 0."""
+    pos = golden("sampler")["pos"]
+    for s in range(len(pos)):
+        assert same_bits(port.rotated_grid(s), pos[s]), s
+    assert np.abs(np.hypot(pos[:, 0], pos[:, 1]) - 0.8).max() < 1e-6
+    sc = scenes["c2_cube"]
+    h = port_scenes["c2_cube"]
+    P = sc.render_params(width=64, height=36, spp=8, seed=3, sampler=1)
+    a, _ = port.render(h, sc, P, nthreads=4)
+    b, _ = port.render(h, sc, P, nthreads=1)
+    assert same_bits(a, b)
+    j, _ = port.render(h, sc, sc.render_params(width=64, height=36, spp=8, seed=3), nthreads=4)
+    assert np.abs(a - j).max() > 0.05
+    lo, _ = port.render(h, sc, sc.render_params(width=64, height=36, spp=8, seed=3, sampler=1, sample_begin=0, sample_count=5), nthreads=4)
+    hi, _ = port.render(h, sc, sc.render_params(width=64, height=36, spp=8, seed=3, sampler=1, sample_begin=5, sample_count=3), nthreads=4)
+    assert np.allclose(lo + hi, a, rtol=1e-5, atol=1e-6)
+
+
+def test_ref_rotated_grid_live(ref, golden):
+    pos = golden("sampler")["pos"]
+    for s in range(len(pos)):
+        assert same_bits(ref.rotated_grid(s), pos[s])
+
+
 def test_philox_known_answers(port):
     """Philox4x32-10 known-answer vectors of the Random123 distribution (kat_vectors): counter, key -> output.
     so_philox maps (seed, pixel, sample, block) to key=(seed lo, hi), counter=(pixel, sample, block, 0)."""
