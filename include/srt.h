@@ -92,7 +92,12 @@ typedef struct srt_material {
   float   roughness;      /* PBR scalar used when roughness_tex < 0                             */
   float   fuzz;           /* METAL (already clamped to <= 1, material.h:89)                     */
   float   ir;             /* DIELECTRIC index of refraction                                     */
+  int32_t flags;          /* SRT_MATF_*; 0 = the reference's behaviour                          */
 } srt_material;
+/* PBR, NOT the reference's behaviour (off unless the loader is told to): metallic_tex is a glTF 2.0
+   metallicRoughnessTexture and IS sampled - metalness = blue/255 * metalness, roughness = green/255 * roughness;
+   roughness_tex is ignored.  (The reference stores this map and never samples it, material.h:78.) */
+#define SRT_MATF_PACKED_MR 1
 
 /* ---- scene ---------------------------------------------------------------------------------- */
 typedef struct srt_scene_desc {
@@ -122,6 +127,13 @@ typedef struct srt_scene_desc {
   const srt_material* materials;
   int32_t             n_tex;
   const srt_texture*  textures;
+  /* optional per-vertex normals, [n_tri*3] each, all three or none (NULL = flat face normals, which is what the reference
+     does: glTF NORMAL is never read, model.h:335-365).  When given, the shading normal of a triangle hit is
+     unit(r0 n0 + r1 n1 + r2 n2) with the reference's own inverse-distance weights r_k (model.h:158-166), NOT the
+     reference's behaviour; frontFace and the tangent basis stay those of the face. */
+  const float*   tri_n0;
+  const float*   tri_n1;
+  const float*   tri_n2;
 } srt_scene_desc;
 
 /* camera: the ten derived members of camera.h:52-62 (private there; the host class exposes them) */

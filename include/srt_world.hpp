@@ -152,7 +152,9 @@ class pbrMetallicRoughness : public material {
   pbrMetallicRoughness(shared_ptr<texture> aMap, vec4f a, float m, float r) : albedoMap(aMap), albedo(a), metalness(m), roughness(r) {}
 
   shared_ptr<texture> albedoMap, normalMap;
-  shared_ptr<texture> metallicRoughnessMap;       // stored, never sampled (material.h:78)
+  shared_ptr<texture> metallicRoughnessMap;       // stored, never sampled (material.h:78) ...
+  bool sampleMetallicRoughnessMap = false;        // ... unless this is set (NOT the reference, SRT_MATF_PACKED_MR in srt.h;
+                                                  // gltfLoad sets it when gltfOptions::sampleMetallicRoughness is on)
   shared_ptr<texture> metallicMap, roughnessMap;
   vec4f albedo = vec4f(1.0f, 1.0f, 1.0f, 1.0f);
   float metalness = 0, roughness = 0, anisotropy = 0;
@@ -209,6 +211,7 @@ class mesh : public hittable {          // model.h:52-76
   std::vector<shared_ptr<triangle>> triangles;
   std::vector<vec3f> positions;
   std::vector<vec2f> texcoords;
+  std::vector<vec3f> normals;           // glTF NORMAL, filled only under gltfOptions::smoothNormals (the reference never reads it)
   shared_ptr<material> matPtr;
  private:
   mesh() = default;
@@ -232,6 +235,11 @@ struct gltfOptions {
                                         //       (model.h:345,361,450), ignore node transforms, 16-bit indices only
                                         // false: honour accessor.byteOffset / byteStride, 8/16/32-bit indices, append to the
                                         //       primitive's own mesh, apply node TRS / matrix transforms to positions
+  // Two things the reference does not do at all, both off by default and independent of referenceQuirks:
+  bool smoothNormals = false;           // read NORMAL into mesh::normals; a scene holding any is shaded with interpolated
+                                        // vertex normals (srt_scene_desc::tri_n0..2); meshes without NORMAL keep face normals
+  bool sampleMetallicRoughness = false; // materials with a metallicRoughnessTexture sample it (glTF 2.0: metal = B * factor,
+                                        // roughness = G * factor) instead of storing it unused (material.h:78)
 };
 gltfOptions& gltfConfig();
 bool gltfLoad(std::string filename, shared_ptr<model> model);
@@ -274,6 +282,7 @@ class flatScene {
   const srt_scene_desc& desc() const { return d; }
   std::string error;
   std::vector<float> tri_v0, tri_v1, tri_v2, tri_uv0, tri_uv1, tri_uv2, sph_c0, sph_c1, sph_t0, sph_t1, sph_r;
+  std::vector<float> tri_n0, tri_n1, tri_n2;         // empty unless some mesh carries vertex normals
   std::vector<int32_t> tri_mat, sph_mat;
   std::vector<srt_bvh_node> nodes;
   std::vector<srt_material> materials;

@@ -61,6 +61,7 @@ static const float PI_F = 3.1415926535897932385f; /* globals.h:15 */
 typedef struct so_scene {
   int64_t n_tri, n_sph, n_nodes;
   float *v0, *v1, *v2, *uv0, *uv1, *uv2; int32_t* tri_mat;
+  float *n0, *n1, *n2;   /* optional per-vertex normals (srt.h: tri_n0), NULL = the reference's flat shading */
   float *c0, *c1, *t0, *t1, *r; int32_t* sph_mat;
   srt_bvh_node* nodes;
   int32_t n_mat, n_tex;
@@ -77,6 +78,7 @@ so_scene* so_scene_create(const srt_scene_desc* d) {
   s->v0 = dup_mem(d->tri_v0, t3); s->v1 = dup_mem(d->tri_v1, t3); s->v2 = dup_mem(d->tri_v2, t3);
   s->uv0 = dup_mem(d->tri_uv0, t2); s->uv1 = dup_mem(d->tri_uv1, t2); s->uv2 = dup_mem(d->tri_uv2, t2);
   s->tri_mat = dup_mem(d->tri_mat, (size_t)d->n_tri * 4);
+  if (d->n_tri > 0 && d->tri_n0 && d->tri_n1 && d->tri_n2) { s->n0 = dup_mem(d->tri_n0, t3); s->n1 = dup_mem(d->tri_n1, t3); s->n2 = dup_mem(d->tri_n2, t3); }
   size_t s3 = (size_t)d->n_sph * 3 * 4, s1 = (size_t)d->n_sph * 4;
   s->c0 = dup_mem(d->sph_c0, s3); s->c1 = dup_mem(d->sph_c1, s3);
   s->t0 = dup_mem(d->sph_t0, s1); s->t1 = dup_mem(d->sph_t1, s1); s->r = dup_mem(d->sph_r, s1);
@@ -96,6 +98,7 @@ so_scene* so_scene_create(const srt_scene_desc* d) {
 
 void so_scene_destroy(so_scene* s) {
   if (!s) return;
+  free(s->n0); free(s->n1); free(s->n2);
   free(s->v0); free(s->v1); free(s->v2); free(s->uv0); free(s->uv1); free(s->uv2); free(s->tri_mat);
   free(s->c0); free(s->c1); free(s->t0); free(s->t1); free(s->r); free(s->sph_mat); free(s->nodes); free(s->mats);
   for (int i = 0; i < s->n_tex; i++) if (s->texs[i].kind == SRT_TEX_IMAGE && s->texs[i].data) free((void*)s->texs[i].data);
@@ -224,6 +227,11 @@ static int triangle_hit(const so_scene* s, int64_t i, const ray_t* r, float tMin
   rec->t = t;
   rec->p = ray_at(r, rec->t);
   set_face_normal(rec, r, outward);
+  if (s->n0) {   /* NOT the reference (srt.h: tri_n0): vertex normals blended with the weights of model.h:158-166 */
+    const float *a = s->n0 + 3 * i, *b = s->n1 + 3 * i, *c = s->n2 + 3 * i;
+    v3 sn = unit_vector(V(r0 * a[0] + r1 * b[0] + r2 * c[0], r0 * a[1] + r1 * b[1] + r2 * c[1], r0 * a[2] + r1 * b[2] + r2 * c[2]));
+    if (sn.x == sn.x && sn.y == sn.y && sn.z == sn.z) rec->normal = rec->front_face ? sn : vneg(sn);
+  }
   rec->u = u; rec->v = v;
   rec->mat = s->tri_mat[i];
   triangle_tangent_basis(s, i, &rec->tangent, &rec->bitangent);
@@ -402,10 +410,16 @@ static int material_scatter(const so_scene* s, const srt_material* m, const ray_
     normal = unit_vector(V(T.x * n.x + (B.x * n.y + N.x * n.z), T.y * n.x + (B.y * n.y + N.y * n.z),
                            T.z * n.x + (B.z * n.y + N.z * n.z)));
   } else normal = rec->normal;
-  if (m->metallic_tex >= 0) mm = clampf(texture_value(s, m->metallic_tex, rec->u, rec->v, rec->p).x / 255.0f, 0, 1.0f);
-  else mm = m->metalness;
-  if (m->roughness_tex >= 0) rr = clampf(texture_value(s, m->roughness_tex, rec->u, rec->v, rec->p).y / 255.0f, 0, 1.0f);
-  else rr = m->roughness;
+  if ((m->flags & SRT_MATF_PACKED_MR) && m->metallic_tex >= 0) {   /* glTF metallicRoughnessTexture: NOT the reference (srt.h) */
+    v3 mr = texture_value(s, m->metallic_tex, rec->u, rec->v, rec->p);
+    mm = clampf(mr.z / 255.0f * m->metalness, 0, 1.0f);
+    rr = clampf(mr.y / 255.0f * m->roughness, 0, 1.0f);
+  } else {
+    if (m->metallic_tex >= 0) mm = clampf(texture_value(s, m->metallic_tex, rec->u, rec->v, rec->p).x / 255.0f, 0, 1.0f);
+    else mm = m->metalness;
+    if (m->roughness_tex >= 0) rr = clampf(texture_value(s, m->roughness_tex, rec->u, rec->v, rec->p).y / 255.0f, 0, 1.0f);
+    else rr = m->roughness;
+  }
 
   v3 sd = vadd(normal, rvec);
   if (((double)fabsf(sd.x) < 1e-8) && ((double)fabsf(sd.y) < 1e-8) && ((double)fabsf(sd.z) < 1e-8)) sd = normal; /* vec3.h:49-52 */

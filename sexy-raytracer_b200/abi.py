@@ -27,7 +27,11 @@ class Texture(C.Structure):
 class Material(C.Structure):
     _fields_ = [("kind", C.c_int32), ("albedo_tex", C.c_int32), ("normal_tex", C.c_int32),
                 ("metallic_tex", C.c_int32), ("roughness_tex", C.c_int32), ("albedo", C.c_float * 4),
-                ("metalness", C.c_float), ("roughness", C.c_float), ("fuzz", C.c_float), ("ir", C.c_float)]
+                ("metalness", C.c_float), ("roughness", C.c_float), ("fuzz", C.c_float), ("ir", C.c_float),
+                ("flags", C.c_int32)]
+
+
+MATF_PACKED_MR = 1
 
 
 class SceneDesc(C.Structure):
@@ -40,7 +44,8 @@ class SceneDesc(C.Structure):
                 ("sph_r", c_float_p), ("sph_mat", c_int32_p),
                 ("n_nodes", C.c_int64), ("nodes", C.POINTER(BvhNode)),
                 ("n_mat", C.c_int32), ("materials", C.POINTER(Material)),
-                ("n_tex", C.c_int32), ("textures", C.POINTER(Texture))]
+                ("n_tex", C.c_int32), ("textures", C.POINTER(Texture)),
+                ("tri_n0", c_float_p), ("tri_n1", c_float_p), ("tri_n2", c_float_p)]
 
 
 class Camera(C.Structure):

@@ -343,6 +343,16 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   SCK(upload(s, tris, &s->sc.tris));
   SCK(upload(s, uvs, &s->sc.tri_uv));
   s->sc.n_tri = (int)d->n_tri;
+  s->sc.tri_vn = nullptr;
+  if (d->n_tri > 0 && (d->tri_n0 || d->tri_n1 || d->tri_n2)) {
+    if (!d->tri_n0 || !d->tri_n1 || !d->tri_n2) { srt_scene_destroy(s); return fail(SRT_ERR_INVALID, "tri_n0, tri_n1, tri_n2: all three or none"); }
+    std::vector<float4> vn((size_t)d->n_tri * 3);
+    for (int64_t i = 0; i < d->n_tri; i++) {
+      const float* n[3] = {d->tri_n0 + 3 * i, d->tri_n1 + 3 * i, d->tri_n2 + 3 * i};
+      for (int k = 0; k < 3; k++) vn[3 * i + k] = make_float4(n[k][0], n[k][1], n[k][2], 0);
+    }
+    SCK(upload(s, vn, &s->sc.tri_vn));
+  }
   std::vector<Sph> sphs((size_t)d->n_sph);
   for (int64_t j = 0; j < d->n_sph; j++) {
     const float *a = d->sph_c0 + 3 * j, *b = d->sph_c1 + 3 * j;
@@ -404,6 +414,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     if (tex_is_image(d, x.albedo_tex) || tex_is_image(d, x.normal_tex) || tex_is_image(d, x.metallic_tex) || tex_is_image(d, x.roughness_tex))
       x.flags |= MAT_NEEDS_UV;
     if (x.normal_tex >= 0) x.flags |= MAT_NEEDS_TBN;
+    if (m.kind == SRT_MAT_PBR && (m.flags & SRT_MATF_PACKED_MR) && x.metallic_tex >= 0) { x.flags |= MAT_PACKED_MR; x.roughness_tex = -1; }
     mats[i] = x;
   }
   SCK(upload(s, mats, &s->sc.mats));

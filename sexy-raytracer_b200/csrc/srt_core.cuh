@@ -73,6 +73,7 @@ struct Tex {
 
 #define MAT_NEEDS_UV  1
 #define MAT_NEEDS_TBN 2
+#define MAT_PACKED_MR 4   // SRT_MATF_PACKED_MR
 struct Mat {
   int kind, albedo_tex, normal_tex, metallic_tex;
   int roughness_tex, flags; float metalness, roughness;
@@ -109,6 +110,7 @@ struct Scene {
   const Node*  nodes;  int n_nodes;
   const Tri*   tris;   int n_tri;
   const TriUV* tri_uv;
+  const float4* tri_vn;  // optional per-vertex normals, 3 x float4 per triangle (srt_scene_desc::tri_n0..2), or nullptr
   const Sph*   sphs;   int n_sph;
   const Mat*   mats;   int n_mat;
   const Tex*   texs;   int n_tex;

@@ -46,15 +46,23 @@ __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ra
   rec.prim = i;
   rec.u = rec.v = 0.0f;
   rec.tangent = rec.bitangent = mk(0, 0, 0);
-  if (want_uv || want_tbn) {
+  const bool smooth = sc.tri_vn != nullptr;
+  if (want_uv || want_tbn || smooth) {
     const float4 ua = __ldg(&sc.tri_uv[i].a), ub = __ldg(&sc.tri_uv[i].b);
-    if (want_uv) {                                                        // model.h:156-169
+    if (want_uv || smooth) {                                              // model.h:156-169
       V3 p = rec.p;
       float d0 = length(p - v0), d1 = length(p - v1), d2 = length(p - v2);
       float denom = (1.0f / d0) + (1.0f / d1) + (1.0f / d2);
       float r0 = (1.0f / d0) / denom, r1 = (1.0f / d1) / denom, r2 = (1.0f / d2) / denom;
-      rec.u = r0 * ua.x + r1 * ua.z + r2 * ub.x;
-      rec.v = 1.0f - (r0 * ua.y + r1 * ua.w + r2 * ub.y);
+      if (want_uv) {
+        rec.u = r0 * ua.x + r1 * ua.z + r2 * ub.x;
+        rec.v = 1.0f - (r0 * ua.y + r1 * ua.w + r2 * ub.y);
+      }
+      if (smooth) {       // not the reference (srt.h: tri_n0): the vertex normals blended with the same weights as the UVs
+        const float4 n0 = __ldg(&sc.tri_vn[3 * (size_t)i]), n1 = __ldg(&sc.tri_vn[3 * (size_t)i + 1]), n2 = __ldg(&sc.tri_vn[3 * (size_t)i + 2]);
+        const V3 s = unit_v<FAST>(mk(r0 * n0.x + r1 * n1.x + r2 * n2.x, r0 * n0.y + r1 * n1.y + r2 * n2.y, r0 * n0.z + r1 * n1.z + r2 * n2.z));
+        if (s.x == s.x && s.y == s.y && s.z == s.z) rec.normal = rec.front_face ? s : -s;   // NaN weights (p on a vertex) keep the face normal
+      }
     }
     if (want_tbn) {                                                       // model.h:214-235
       V3 e0 = v1 - v0, e1 = v2 - v0;
@@ -199,10 +207,16 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
     normal = unit_v<FAST>(mk(T.x * n.x + (B.x * n.y + N.x * n.z), T.y * n.x + (B.y * n.y + N.y * n.z),
                             T.z * n.x + (B.z * n.y + N.z * n.z)));
   } else normal = rec.normal;
-  if (m.metallic_tex >= 0) mm = clampf(texture_value(sc, m.metallic_tex, rec.u, rec.v, rec.p).x / 255.0f, 0, 1.0f);
-  else mm = m.metalness;
-  if (m.roughness_tex >= 0) rr = clampf(texture_value(sc, m.roughness_tex, rec.u, rec.v, rec.p).y / 255.0f, 0, 1.0f);
-  else rr = m.roughness;
+  if ((m.flags & MAT_PACKED_MR) && m.metallic_tex >= 0) {     // glTF metallicRoughnessTexture, not the reference (srt.h)
+    const V3 mr = texture_value(sc, m.metallic_tex, rec.u, rec.v, rec.p);
+    mm = clampf(mr.z / 255.0f * m.metalness, 0, 1.0f);
+    rr = clampf(mr.y / 255.0f * m.roughness, 0, 1.0f);
+  } else {
+    if (m.metallic_tex >= 0) mm = clampf(texture_value(sc, m.metallic_tex, rec.u, rec.v, rec.p).x / 255.0f, 0, 1.0f);
+    else mm = m.metalness;
+    if (m.roughness_tex >= 0) rr = clampf(texture_value(sc, m.roughness_tex, rec.u, rec.v, rec.p).y / 255.0f, 0, 1.0f);
+    else rr = m.roughness;
+  }
 
   V3 sd = normal + rvec;
   // vec3.h:49-52 compares fabs() < 1e-8 in double; (double)x < 1e-8  <=>  x <= fl32(1e-8)

@@ -105,6 +105,8 @@ def scene_from_desc(d):
     s.tri_v0, s.tri_v1, s.tri_v2 = (arr(p, nt, 3, np.float32) for p in (d.tri_v0, d.tri_v1, d.tri_v2))
     s.tri_uv0, s.tri_uv1, s.tri_uv2 = (arr(p, nt, 2, np.float32) for p in (d.tri_uv0, d.tri_uv1, d.tri_uv2))
     s.tri_mat = arr(d.tri_mat, nt, 1, np.int32)
+    if nt and d.tri_n0:
+        s.tri_n0, s.tri_n1, s.tri_n2 = (arr(p, nt, 3, np.float32) for p in (d.tri_n0, d.tri_n1, d.tri_n2))
     s.sph_c0, s.sph_c1 = arr(d.sph_c0, ns, 3, np.float32), arr(d.sph_c1, ns, 3, np.float32)
     s.sph_t0, s.sph_t1, s.sph_r = (arr(p, ns, 1, np.float32) for p in (d.sph_t0, d.sph_t1, d.sph_r))
     s.sph_mat = arr(d.sph_mat, ns, 1, np.int32)
@@ -118,6 +120,9 @@ def scene_from_desc(d):
     s.mat_albedo = np.array([list(d.materials[i].albedo) for i in range(nm)], np.float32).reshape(nm, 4)
     s.mat_params = np.array([[d.materials[i].metalness, d.materials[i].roughness, d.materials[i].fuzz, d.materials[i].ir]
                              for i in range(nm)], np.float32).reshape(nm, 4)
+    flags = np.array([d.materials[i].flags for i in range(nm)], np.int32)
+    if flags.any():
+        s.mat_flags = flags
     s.tex_kind = np.array([d.textures[i].kind for i in range(nx)], np.int32)
     s.tex_color = np.array([list(d.textures[i].color) for i in range(nx)], np.float32).reshape(nx, 3)
     s.tex_evenodd = np.array([[d.textures[i].even, d.textures[i].odd] for i in range(nx)], np.int32).reshape(nx, 2)
@@ -144,11 +149,13 @@ def reference_scene(which, data_dir):
         L.srt_host_scene_free(h)
 
 
-def gltf_scene(path, texture_dir=None, reference_quirks=True):
-    """A glTF / GLB file through model::create(...)->init() + bvhNode + flatScene -> Scene (triangles only)."""
+def gltf_scene(path, texture_dir=None, reference_quirks=True, smooth_normals=False, sample_metallic_roughness=False):
+    """A glTF / GLB file through model::create(...)->init() + bvhNode + flatScene -> Scene (triangles only).  The last two
+    options are not reference behaviour (include/srt_world.hpp: gltfOptions)."""
     L = _bind_world(lib())
     h = C.c_void_p()
-    _check(L.srt_host_scene_gltf(os.fsencode(path), os.fsencode(texture_dir) if texture_dir else None, int(reference_quirks), C.byref(h)))
+    opts = (1 if reference_quirks else 0) | (2 if smooth_normals else 0) | (4 if sample_metallic_roughness else 0)
+    _check(L.srt_host_scene_gltf(os.fsencode(path), os.fsencode(texture_dir) if texture_dir else None, opts, C.byref(h)))
     try:
         return scene_from_desc(L.srt_host_scene_desc(h).contents)
     finally:

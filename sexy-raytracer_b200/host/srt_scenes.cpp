@@ -146,13 +146,15 @@ srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_sc
   return SRT_OK;
 }
 
-srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int reference_quirks, srt_host_scene** out) {
+srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int options, srt_host_scene** out) {
   if (!out || !gltf_path) return fail(SRT_ERR_INVALID, "NULL argument");
   *out = nullptr;
   auto* S = new srt_host_scene;
   const gltfOptions saved = gltfConfig();
   if (texture_dir) gltfConfig().textureDir = texture_dir;
-  gltfConfig().referenceQuirks = reference_quirks != 0;
+  gltfConfig().referenceQuirks = (options & SRT_GLTF_REFERENCE_QUIRKS) != 0;
+  gltfConfig().smoothNormals = (options & SRT_GLTF_SMOOTH_NORMALS) != 0;
+  gltfConfig().sampleMetallicRoughness = (options & SRT_GLTF_SAMPLE_MR) != 0;
   hittableList objects;
   bool ok = true;
   addModel(objects, S->models, gltf_path, ok);

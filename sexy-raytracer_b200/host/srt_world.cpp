@@ -231,6 +231,9 @@ struct Tables {
       r.metallic_tex = tex(p->metallicMap); r.roughness_tex = tex(p->roughnessMap);
       for (int k = 0; k < 4; k++) r.albedo[k] = p->albedo(k);
       r.metalness = p->metalness; r.roughness = p->roughness;
+      if (p->sampleMetallicRoughnessMap && p->metallicRoughnessMap) {      // not the reference: SRT_MATF_PACKED_MR
+        r.metallic_tex = tex(p->metallicRoughnessMap); r.roughness_tex = -1; r.flags |= SRT_MATF_PACKED_MR;
+      }
     } else if (auto q = dynamic_cast<const metal*>(m.get())) {
       r.kind = SRT_MAT_METAL;
       for (int k = 0; k < 3; k++) r.albedo[k] = q->albedo(k);
@@ -270,10 +273,35 @@ bool flatScene::build(const hittableList& world) {
   tri_v0.swap(soa.v0); tri_v1.swap(soa.v1); tri_v2.swap(soa.v2); tri_uv0.swap(soa.uv0); tri_uv1.swap(soa.uv1); tri_uv2.swap(soa.uv2);
   sph_c0.swap(soa.c0); sph_c1.swap(soa.c1); sph_t0.swap(soa.t0); sph_t1.swap(soa.t1); sph_r.swap(soa.r);
   nodes = root->nodes;
+  // vertex normals, when any mesh has them; triangles of meshes without get their face normal three times
+  tri_n0.clear(); tri_n1.clear(); tri_n2.clear();
+  bool any_normals = false;
+  for (const triangle* t : soa.tris) if (!t->parentMesh.lock()->normals.empty()) { any_normals = true; break; }
+  if (any_normals) {
+    std::vector<float>* N[3] = {&tri_n0, &tri_n1, &tri_n2};
+    for (size_t i = 0; i < soa.tris.size(); i++) {
+      const triangle* t = soa.tris[i];
+      const auto m = t->parentMesh.lock();
+      const bool has = t->vertices[0] < m->normals.size() && t->vertices[1] < m->normals.size() && t->vertices[2] < m->normals.size();
+      float fn[3] = {0, 0, 0};
+      if (!has) {
+        const float *a = &tri_v0[3 * i], *b = &tri_v1[3 * i], *c = &tri_v2[3 * i];
+        const double e0[3] = {(double)b[0] - a[0], (double)b[1] - a[1], (double)b[2] - a[2]}, e1[3] = {(double)c[0] - a[0], (double)c[1] - a[1], (double)c[2] - a[2]};
+        const double n[3] = {e0[1] * e1[2] - e0[2] * e1[1], e0[2] * e1[0] - e0[0] * e1[2], e0[0] * e1[1] - e0[1] * e1[0]};
+        const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        for (int k = 0; k < 3; k++) fn[k] = len > 0 ? (float)(n[k] / len) : 0.0f;
+      }
+      for (int k = 0; k < 3; k++) {
+        const float* src = has ? m->normals[t->vertices[k]].d : fn;
+        N[k]->insert(N[k]->end(), src, src + 3);
+      }
+    }
+  }
   memset(&d, 0, sizeof d);
   d.n_tri = (int64_t)tri_mat.size();
   d.tri_v0 = tri_v0.data(); d.tri_v1 = tri_v1.data(); d.tri_v2 = tri_v2.data();
   d.tri_uv0 = tri_uv0.data(); d.tri_uv1 = tri_uv1.data(); d.tri_uv2 = tri_uv2.data(); d.tri_mat = tri_mat.data();
+  if (any_normals) { d.tri_n0 = tri_n0.data(); d.tri_n1 = tri_n1.data(); d.tri_n2 = tri_n2.data(); }
   d.n_sph = (int64_t)sph_mat.size();
   d.sph_c0 = sph_c0.data(); d.sph_c1 = sph_c1.data(); d.sph_t0 = sph_t0.data(); d.sph_t1 = sph_t1.data(); d.sph_r = sph_r.data();
   d.sph_mat = sph_mat.data();
@@ -500,6 +528,33 @@ bool gltfLoad(std::string filename, shared_ptr<model> mdl) {
               }
               target->positions.push_back(vec3f(v[0], v[1], v[2]));
             }
+          } else if (name == "NORMAL" && g_gltf.smoothNormals) {          // never read by the reference (model.h:335-365)
+            if (!g.view((long)kv.second.num, 12, ptr, stride, count, acc)) return false;
+            if (acc->string("type") != "VEC3") continue;
+            const Mat4* xf = (!g_gltf.referenceQuirks && mesh_xf.count((long)meshIndex)) ? &mesh_xf[(long)meshIndex] : nullptr;
+            double it[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};                   // inverse transpose of the upper 3x3, row-major
+            if (xf) {
+              const double a = xf->m[0], b = xf->m[4], c = xf->m[8], d2 = xf->m[1], e = xf->m[5], f = xf->m[9], g2 = xf->m[2], h = xf->m[6], i2 = xf->m[10];
+              const double det = a * (e * i2 - f * h) - b * (d2 * i2 - f * g2) + c * (d2 * h - e * g2);
+              if (det != 0) {
+                const double inv[9] = {(e * i2 - f * h) / det, (c * h - b * i2) / det, (b * f - c * e) / det,
+                                       (f * g2 - d2 * i2) / det, (a * i2 - c * g2) / det, (c * d2 - a * f) / det,
+                                       (d2 * h - e * g2) / det, (b * g2 - a * h) / det, (a * e - b * d2) / det};
+                for (int r = 0; r < 3; r++) for (int q = 0; q < 3; q++) it[3 * r + q] = inv[3 * q + r];
+              }
+            }
+            for (size_t k = 0; k < count; k++) {
+              float v[3];
+              memcpy(v, ptr + k * stride, 12);
+              if (xf) {
+                const double x = v[0], y = v[1], z = v[2];
+                double o[3];
+                for (int r = 0; r < 3; r++) o[r] = it[3 * r] * x + it[3 * r + 1] * y + it[3 * r + 2] * z;
+                const double len = std::sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]);
+                for (int r = 0; r < 3; r++) v[r] = (float)(len > 0 ? o[r] / len : o[r]);
+              }
+              target->normals.push_back(vec3f(v[0], v[1], v[2]));
+            }
           } else if (base == "TEXCOORD") {
             if (!g_gltf.referenceQuirks && name != "TEXCOORD_0") continue;
             if (!g.view((long)kv.second.num, 8, ptr, stride, count, acc)) return false;
@@ -531,7 +586,9 @@ bool gltfLoad(std::string filename, shared_ptr<model> mdl) {
           if (!textureFile.empty()) albedoPNG = make_shared<imagePNG>(textureFile.c_str(), 3);
           if (!normalMapFile.empty()) normalPNG = make_shared<imagePNG>(normalMapFile.c_str(), 3);
           if (!mrFile.empty()) mrPNG = make_shared<imagePNG>(mrFile.c_str(), 3);
-          newMesh->matPtr = make_shared<pbrMetallicRoughness>(albedoPNG, normalPNG, mrPNG, baseColor, metallicness, roughness);
+          auto pm = make_shared<pbrMetallicRoughness>(albedoPNG, normalPNG, mrPNG, baseColor, metallicness, roughness);
+          pm->sampleMetallicRoughnessMap = g_gltf.sampleMetallicRoughness && mrPNG != nullptr;
+          newMesh->matPtr = pm;
         }
       }
 

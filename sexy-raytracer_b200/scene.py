@@ -26,6 +26,8 @@ class Scene:
               "sph_c0", "sph_c1", "sph_t0", "sph_t1", "sph_r", "sph_mat", "nodes",
               "mat_kind", "mat_tex", "mat_albedo", "mat_params",
               "tex_kind", "tex_color", "tex_evenodd", "tex_whb", "tex_missing")
+    # not the reference's behaviour, absent from files that do not use them
+    OPTIONAL = ("tri_n0", "tri_n1", "tri_n2", "mat_flags")
 
     def __init__(self):
         self.tri_v0 = self.tri_v1 = self.tri_v2 = np.zeros((0, 3), _F)
@@ -45,6 +47,8 @@ class Scene:
         self.tex_whb = np.zeros((0, 3), _I)       # width, height, bytes per texel
         self.tex_missing = np.zeros(0, _I)        # 1 = image file was missing (data NULL)
         self.tex_data = {}                        # texture id -> uint8 array [h*w*bpp]
+        self.tri_n0 = self.tri_n1 = self.tri_n2 = None   # per-vertex normals [n_tri,3], all three or none
+        self.mat_flags = None                     # [n_mat] abi.MATF_*, None = all 0
         # config
         self.camera = np.zeros(24, _F)            # srt_camera, flat
         self.cam_args = np.zeros(15, _F)          # eye3 lookAt3 up3 vfov aspect aperture focus t0 t1
@@ -69,6 +73,7 @@ class Scene:
     def host_bytes(self):
         """Bytes handed across the ABI by srt_scene_create (the H2D volume of one scene upload)."""
         n = sum(getattr(self, k).nbytes for k in self.ARRAYS)
+        n += sum(getattr(self, k).nbytes for k in self.OPTIONAL if getattr(self, k) is not None)
         return int(n + sum(v.nbytes for v in self.tex_data.values()))
 
     # ---- C view
@@ -89,6 +94,9 @@ class Scene:
         d.tri_v0, d.tri_v1, d.tri_v2 = fp(self.tri_v0), fp(self.tri_v1), fp(self.tri_v2)
         d.tri_uv0, d.tri_uv1, d.tri_uv2 = fp(self.tri_uv0), fp(self.tri_uv1), fp(self.tri_uv2)
         d.tri_mat = ip(self.tri_mat)
+        if self.tri_n0 is not None:
+            assert all(np.shape(x) == (self.n_tri, 3) for x in (self.tri_n0, self.tri_n1, self.tri_n2))
+            d.tri_n0, d.tri_n1, d.tri_n2 = fp(self.tri_n0), fp(self.tri_n1), fp(self.tri_n2)
         d.n_sph = self.n_sph
         d.sph_c0, d.sph_c1 = fp(self.sph_c0), fp(self.sph_c1)
         d.sph_t0, d.sph_t1, d.sph_r = fp(self.sph_t0), fp(self.sph_t1), fp(self.sph_r)
@@ -104,6 +112,7 @@ class Scene:
             m.albedo_tex, m.normal_tex, m.metallic_tex, m.roughness_tex = (int(x) for x in self.mat_tex[i])
             m.albedo[:] = [float(x) for x in self.mat_albedo[i]]
             m.metalness, m.roughness, m.fuzz, m.ir = (float(x) for x in self.mat_params[i])
+            m.flags = int(self.mat_flags[i]) if self.mat_flags is not None else 0
         d.n_mat, d.materials = nm, mats
         nt = self.tex_kind.shape[0]
         texs = (abi.Texture * max(nt, 1))()
@@ -139,6 +148,7 @@ class Scene:
     # ---- persistence
     def save(self, path):
         d = {k: getattr(self, k) for k in self.ARRAYS}
+        d.update({k: getattr(self, k) for k in self.OPTIONAL if getattr(self, k) is not None})
         # identical images (the same PNG loaded by several materials) are stored once
         blobs, ref = [], np.full(self.tex_kind.shape[0], -1, _I)
         for i, a in sorted(self.tex_data.items()):
@@ -162,6 +172,9 @@ class Scene:
         with np.load(path, allow_pickle=False) as z:
             for k in cls.ARRAYS:
                 setattr(s, k, z[k])
+            for k in cls.OPTIONAL:
+                if k in z.files:
+                    setattr(s, k, z[k])
             ref = z["tex_blob_ref"]
             blobs = {}
             for i, k in enumerate(ref):

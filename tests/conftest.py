@@ -42,6 +42,38 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def ext_scene(scenes):
+    """Config 3's scene with the two things the reference does not do switched on: per-vertex normals
+    (the face normal bent towards the direction from the mesh's centroid to the vertex) and, for every textured PBR material,
+    its base-colour image used as a packed metallicRoughnessTexture (SRT_MATF_PACKED_MR) with factors 0.9 / 0.8."""
+    import copy
+    from sexy_raytracer_b200 import abi
+    s = copy.copy(scenes["c3_masterchief"])
+    F = np.float32
+    v = [s.tri_v0.astype(np.float64), s.tri_v1.astype(np.float64), s.tri_v2.astype(np.float64)]
+    fn = np.cross(v[1] - v[0], v[2] - v[0])
+    fn /= np.maximum(np.linalg.norm(fn, axis=1, keepdims=True), 1e-30)
+    cen = np.concatenate(v).mean(axis=0)
+    out = []
+    for k in range(3):
+        d = v[k] - cen
+        d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-30)
+        n = fn + 0.6 * d
+        out.append((n / np.linalg.norm(n, axis=1, keepdims=True)).astype(F))
+    s.tri_n0, s.tri_n1, s.tri_n2 = out
+    s.mat_tex = s.mat_tex.copy(); s.mat_params = s.mat_params.copy()
+    s.mat_flags = np.zeros(len(s.mat_kind), np.int32)
+    for i in range(len(s.mat_kind)):
+        a = int(s.mat_tex[i, 0])
+        if s.mat_kind[i] == abi.SRT_MAT_PBR and a >= 0 and s.tex_kind[a] == abi.SRT_TEX_IMAGE and s.tex_whb[a, 2] == 3:
+            s.mat_tex[i, 2], s.mat_tex[i, 3] = a, -1
+            s.mat_params[i, 0], s.mat_params[i, 1] = 0.9, 0.8
+            s.mat_flags[i] = abi.MATF_PACKED_MR
+    assert s.mat_flags.any()
+    return s
+
+
+@pytest.fixture(scope="session")
 def port():
     """The plain-C restatement (checker).  Built on demand: gcc is part of the image."""
     from oracle import refbind

@@ -129,6 +129,61 @@ def test_ref_rotated_grid_live(ref, golden):
         assert same_bits(ref.rotated_grid(s), pos[s])
 
 
+def test_port_smooth_normals_and_packed_mr(port, scenes, ext_scene):
+    """The two non-reference options of srt.h (tri_n0..2, SRT_MATF_PACKED_MR) in the port, against numpy restatements:
+    the shading normal is unit(sum r_k n_k) with the inverse-distance weights of model.h:158-166, ids / t / uv / tangent basis
+    are untouched; a packed map gives metalness = B/255 * factor, roughness = G/255 * factor - checked against a scene whose
+    material carries those two numbers as scalars, texel by texel."""
+    base = scenes["c3_masterchief"]
+    rays = rayset.pinhole(base, step=3)
+    hb, he = port.from_scene(base), port.from_scene(ext_scene)
+    a, b = port.trace(hb, rays), port.trace(he, rays)
+    for f in ("prim", "mat", "front_face", "t", "p", "uv", "tangent", "bitangent"):
+        assert same_bits(a[f], b[f]), f
+    tri = (a["prim"] >= 0) & (a["prim"] < base.n_tri)
+    assert tri.sum() > 500
+    assert same_bits(a["normal"][~tri], b["normal"][~tri])
+    F = np.float32
+    i = a["prim"][tri]
+    p = a["p"][tri]
+    w = [F(1) / np.sqrt((((p - v[i]) ** 2).astype(F)).sum(axis=1, dtype=np.float64)).astype(F) for v in (base.tri_v0, base.tri_v1, base.tri_v2)]
+    den = (w[0] + w[1] + w[2]).astype(F)
+    r = [(x / den).astype(F) for x in w]
+    n = r[0][:, None] * ext_scene.tri_n0[i] + r[1][:, None] * ext_scene.tri_n1[i] + r[2][:, None] * ext_scene.tri_n2[i]
+    n = n / np.linalg.norm(n, axis=1, keepdims=True)
+    assert np.abs(b["normal"][tri] - n).max() < 2e-5
+    assert np.abs(b["normal"][tri] - a["normal"][tri]).max() > 0.05
+    # packed metallic-roughness: shade the flat-normal hits with the packed map, then with per-hit scalars
+    import copy
+    flat = copy.copy(ext_scene)
+    flat.tri_n0 = flat.tri_n1 = flat.tri_n2 = None
+    hf = port.from_scene(flat)
+    sel = np.flatnonzero(tri)[:400]
+    rng = np.random.default_rng(11)
+    rv = rng.normal(size=(len(sel), 3))
+    xi = np.concatenate([rv / np.linalg.norm(rv, axis=1, keepdims=True), rng.random((len(sel), 1))], axis=1).astype(F)
+    att, _, out, sc = port.shade_kat(hf, rays[sel], a[sel], xi)
+    att0, _, _, _ = port.shade_kat(hb, rays[sel], a[sel], xi)
+    assert np.abs(att - att0).max() > 1e-3
+    for k in range(0, len(sel), 40):
+        hit = a[sel[k]]
+        m = int(hit["mat"])
+        assert flat.mat_flags[m] == 1
+        tex = int(flat.mat_tex[m, 2])
+        texel = port.texture_kat(hf, tex, np.array([[hit["uv"][0], hit["uv"][1], 0, 0, 0]], F))[0]
+        one = copy.copy(flat)
+        one.mat_tex = flat.mat_tex.copy(); one.mat_params = flat.mat_params.copy(); one.mat_flags = None
+        one.mat_tex[m, 2] = -1
+        one.mat_params[m, 0] = min(max(F(texel[2]) / F(255) * flat.mat_params[m, 0], F(0)), F(1))
+        one.mat_params[m, 1] = min(max(F(texel[1]) / F(255) * flat.mat_params[m, 1], F(0)), F(1))
+        h1 = port.from_scene(one)
+        att1, _, out1, _ = port.shade_kat(h1, rays[sel[k]:sel[k] + 1], a[sel[k]:sel[k] + 1], xi[k:k + 1])
+        port.free(h1)
+        assert same_bits(att1[0], att[k]) and same_bits(out1, out[k:k + 1])
+    for h in (hb, he, hf):
+        port.free(h)
+
+
 def test_philox_known_answers(port):
     """Philox4x32-10 known-answer vectors of the Random123 distribution (kat_vectors): counter, key -> output.
     so_philox maps (seed, pixel, sample, block) to key=(seed lo, hi), counter=(pixel, sample, block, 0)."""

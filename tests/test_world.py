@@ -219,6 +219,47 @@ def test_gltf_reader_quirks_and_fixes(tmp_path):
         host.gltf_scene(str(bad))
 
 
+def test_gltf_smooth_normals_and_metallic_roughness_options(tmp_path):
+    """SURVEY 8.6 next-3, the two things the reference never does: NORMAL is read (and carried through node transforms by the
+    inverse transpose) only under smoothNormals; a metallicRoughnessTexture is sampled only under sampleMetallicRoughness.
+    With both off the flattened scene is what the reference's loader would give."""
+    path, pos, _ = _tiny_gltf(tmp_path, name="n")
+    doc = json.loads(open(path).read())
+    nrm = np.array([[0, 0, 1], [0.6, 0, 0.8], [0, 0.6, 0.8], [-0.6, 0, 0.8]], np.float32)
+    blob = base64.b64decode(doc["buffers"][0]["uri"].split(",", 1)[1])
+    off = len(blob)
+    blob += nrm.tobytes()
+    doc["buffers"][0] = {"byteLength": len(blob), "uri": "data:application/octet-stream;base64," + base64.b64encode(blob).decode()}
+    doc["bufferViews"].append({"buffer": 0, "byteOffset": off, "byteLength": nrm.nbytes})
+    doc["accessors"].append({"bufferView": 3, "componentType": 5126, "count": 4, "type": "VEC3"})
+    doc["meshes"][0]["primitives"][0]["attributes"]["NORMAL"] = 3
+    doc["nodes"][0]["scale"] = [2.0, 1.0, 1.0]
+    mr = np.zeros((2, 2, 3), np.uint8)
+    mr[..., 1], mr[..., 2] = [[10, 20], [30, 40]], [[200, 210], [220, 230]]
+    host.png_write(str(tmp_path / "mr.png"), mr)
+    doc["images"] = [{"uri": "mr.png"}]
+    doc["textures"] = [{"source": 0}]
+    doc["materials"][0]["pbrMetallicRoughness"]["metallicRoughnessTexture"] = {"index": 0}
+    open(path, "w").write(json.dumps(doc))
+    tex_dir = str(tmp_path) + "/"
+    plain = host.gltf_scene(path, tex_dir, reference_quirks=False)
+    assert plain.tri_n0 is None and plain.mat_flags is None and plain.mat_tex[0].tolist() == [-1, -1, -1, -1]
+    s = host.gltf_scene(path, tex_dir, reference_quirks=False, smooth_normals=True, sample_metallic_roughness=True)
+    assert _same(s.tri_v0, plain.tri_v0) and _same(s.nodes, plain.nodes)
+    want = nrm.astype(np.float64) / np.array([2.0, 1.0, 1.0])          # inverse transpose of diag(2,1,1)
+    want = (want / np.linalg.norm(want, axis=1, keepdims=True)).astype(np.float32)
+    assert np.allclose(s.tri_n0, want[[0, 0]], atol=1e-6) and np.allclose(s.tri_n1, want[[1, 2]], atol=1e-6)
+    assert np.allclose(s.tri_n2, want[[2, 3]], atol=1e-6)
+    assert s.mat_flags.tolist() == [abi.MATF_PACKED_MR]
+    t = int(s.mat_tex[0, 2])
+    assert t >= 0 and s.mat_tex[0, 3] == -1 and s.tex_whb[t].tolist() == [2, 2, 3]
+    assert np.array_equal(np.asarray(s.tex_data[t]).reshape(2, 2, 3), mr)
+    assert s.mat_params[0, 0] == 0.5 and s.mat_params[0, 1] == 0.125     # the factors still multiply
+    # under the reference's quirks the normals are read the same way, without the node transform
+    q = host.gltf_scene(path, tex_dir, reference_quirks=True, smooth_normals=True)
+    assert np.allclose(q.tri_n1, nrm[[1, 2]], atol=1e-7) and q.mat_flags is None
+
+
 @needs_ref_data
 def test_gltf_reference_assets_both_modes():
     """The reference's own assets carry no accessor offsets / strides / node transforms that matter, so both modes agree."""
