@@ -259,6 +259,9 @@ k_wf_extend(Scene sc, WfPool pool, WfCursors* cur, int th_walk,
   }
 }
 
+#ifndef SRT_SHADE_PREFETCH
+#define SRT_SHADE_PREFETCH 1
+#endif
 #ifndef SRT_SHADE_MIN_BLOCKS
 #define SRT_SHADE_MIN_BLOCKS 4   /* 64 registers, 52 B of spills: 4 CTAs per SM measured +3-4 % per frame over 3 (80 registers) */
 #endif
@@ -399,6 +402,21 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
   for (int chunk = blockIdx.x; chunk * CH < pool.n_slots; chunk += gridDim.x) {
     const int base = chunk * CH;
     if (threadIdx.x == 0) { s_nhit = 0; s_nfree = 0; }
+#if SRT_SHADE_PREFETCH
+    {   // the block's next chunk: pull its 6 x 512 records towards the L2 while this chunk is served (they stream from HBM)
+      const long long nb = (long long)(chunk + (int)gridDim.x) * CH;
+      if (nb + CH <= (long long)pool.n_slots) {
+        const int a = threadIdx.x >> 6, line = threadIdx.x & 63;               // four 16-byte arrays x 64 lines of 128 bytes
+        const float4* p16 = a == 0 ? pool.thr : a == 1 ? pool.ray_o : a == 2 ? pool.ray_d : pool.rad;
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(p16 + nb + line * 8));
+        if (threadIdx.x < 64) {                                                // two 8-byte arrays x 32 lines
+          const int l8 = threadIdx.x & 31;
+          const void* p8 = threadIdx.x < 32 ? (const void*)(pool.hit + nb + l8 * 16) : (const void*)(pool.id + nb + l8 * 16);
+          asm volatile("prefetch.global.L2 [%0];" :: "l"(p8));
+        }
+      }
+    }
+#endif
     __syncthreads();
     // ---- pass 0: classify (two slots per thread)
 #pragma unroll
