@@ -9,6 +9,8 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "srt_kernels.cuh"
 #include "srt_phased.cuh"
 #include "srt_wavefront.cuh"
@@ -45,6 +47,8 @@ struct srt_device {
   cudaEvent_t wf_ev[8] = {};
   cudaEvent_t wf_t[16][3] = {};               // per-wave timing ring: before shade, after shade, after extend
   float2* d_grid = nullptr; size_t grid_cap = 0;   // srt_render_params::sampler == 1 (srt_launch.cuh: ensure_grid)
+  unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
+  void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
 };
 static const int WF_RING = 8;
 static const int WF_TRING = 16;
@@ -58,6 +62,7 @@ struct srt_scene {
   int64_t bytes = 0;
   int nodes_in_smem = 0;
   size_t node_bytes = 0;
+  float root_lo[3] = {0, 0, 0}, root_hi[3] = {0, 0, 0};   // node 0's box
 };
 
 extern "C" {
@@ -103,6 +108,8 @@ void srt_device_destroy(srt_device* d) {
   cudaSetDevice(d->gpu);
   if (d->d_counters) cudaFree(d->d_counters);
   if (d->d_grid) cudaFree(d->d_grid);
+  if (d->d_sort) cudaFree(d->d_sort);
+  if (d->d_sort_tmp) cudaFree(d->d_sort_tmp);
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
@@ -274,6 +281,11 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   s->sc.n_nodes = n_real;
   s->sc.filter_ok = filter_ok ? 1 : 0;
   s->node_bytes = (size_t)(n_real + 1) * sizeof(Node);
+  if (n_real > 0) {
+    const Node& r0 = nodes[0];
+    s->root_lo[0] = r0.lo.x; s->root_lo[1] = r0.lo.y; s->root_lo[2] = r0.lo.z;
+    s->root_hi[0] = r0.lo.w; s->root_hi[1] = r0.hi.x; s->root_hi[2] = r0.hi.y;
+  }
   s->nodes_in_smem = s->node_bytes > 0 && s->node_bytes <= dev->smem_optin;
   if (const char* f = getenv("SRT_FORCE_GLOBAL_TREE")) if (atoi(f)) s->nodes_in_smem = 0;   // tests: small scenes through the HBM paths
 

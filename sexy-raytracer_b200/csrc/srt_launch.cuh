@@ -107,7 +107,9 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
       plan.wf_shade = sorted ? (dev->counters ? (const void*)k_wf_shade2<true> : (const void*)k_wf_shade2<false>)
                              : (dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>);
     }
-    e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dev->smem_optin);
+    cudaFuncAttributes fa{};
+    e = cudaFuncGetAttributes(&fa, plan.fn);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(dev->smem_optin - fa.sharedSizeBytes));
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
   } else if (plan.variant == 3) {
     // SRT_TUNE="threads,th_shade,th_leaf,th_trav" (tuning sweeps only; results do not depend on it)
@@ -178,6 +180,33 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     pool.hit = (int2*)b;     b += C * sizeof(int2);
     pool.id = (uint2*)b;
     pool.n_slots = (int)N;
+    pool.order = nullptr;
+  }
+  // ray ordering (srt_wavefront.cuh: k_wf_keys) for trees in HBM; SRT_WF_SORT=0|1 overrides (A/B runs)
+  bool sort_rays = !s->nodes_in_smem && s->node_bytes > dev->l2_bytes;
+  if (const char* e = getenv("SRT_WF_SORT")) sort_rays = atoi(e) != 0;
+  WfSortGrid grid{};
+  if (const char* e = getenv("SRT_WF_KEY")) grid.mode = atoi(e);
+  unsigned *keys_in = nullptr, *keys_out = nullptr, *vals_in = nullptr, *vals_out = nullptr;
+  if (sort_rays) {
+    if (dev->sort_cap < N) {
+      if (dev->d_sort) { CK(cudaFree(dev->d_sort)); dev->d_sort = nullptr; dev->sort_cap = 0; }
+      if (dev->d_sort_tmp) { CK(cudaFree(dev->d_sort_tmp)); dev->d_sort_tmp = nullptr; dev->sort_tmp_bytes = 0; }
+      cudaError_t e = cudaMalloc(&dev->d_sort, 4 * N * sizeof(unsigned));
+      if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_NOMEM, "ray-order buffers: " + std::string(cudaGetErrorString(e))); }
+      dev->sort_cap = N;
+      size_t tmp = 0;
+      CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const unsigned*)nullptr, (unsigned*)nullptr, (const unsigned*)nullptr,
+                                         (unsigned*)nullptr, (int)N, 0, 28, dev->stream));
+      CK(cudaMalloc(&dev->d_sort_tmp, tmp));
+      dev->sort_tmp_bytes = tmp;
+    }
+    keys_in = dev->d_sort; keys_out = keys_in + dev->sort_cap; vals_in = keys_out + dev->sort_cap; vals_out = vals_in + dev->sort_cap;
+    for (int k = 0; k < 3; k++) {
+      const float lo = s->root_lo[k], ext = s->root_hi[k] - s->root_lo[k];
+      grid.org[k] = lo; grid.inv_cell[k] = ext > 0 ? 256.0f / ext : 0.0f;
+    }
+    pool.order = vals_out;
   }
   const unsigned long long total = (unsigned long long)plan.A.n_tiles * 32ull * (unsigned long long)plan.A.sample_count;
   Scene sc = s->sc; RenderArgs A = plan.A; WfCursors* cur = dev->d_wf_cur; unsigned long long* ctr = dev->d_counters;
@@ -224,6 +253,13 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     CK(cudaEventRecord(t[1], dev->stream));
     CK(cudaMemcpyAsync(&dev->h_wf_ring[j % WF_RING], cur, sizeof(WfCursors), cudaMemcpyDeviceToHost, dev->stream));
     CK(cudaEventRecord(dev->wf_ev[j % WF_RING], dev->stream));
+    if (sort_rays) {
+      k_wf_keys<<<reset_blocks, 256, 0, dev->stream>>>(pool, grid, keys_in, vals_in);
+      size_t tmp = dev->sort_tmp_bytes;
+      CK(cub::DeviceRadixSort::SortPairs(dev->d_sort_tmp, tmp, (const unsigned*)keys_in, keys_out, (const unsigned*)vals_in, vals_out,
+                                         (int)N, 0, 28, dev->stream));
+      ++launches;                                        // k_wf_keys; the library's sort passes are not counted as ours
+    }
     CK(cudaLaunchKernel(plan.fn, dim3(plan.blocks), dim3(plan.threads), extend_args, plan.smem, dev->stream));
     CK(cudaEventRecord(t[2], dev->stream));
     launches += 2; ++waves;

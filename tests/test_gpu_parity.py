@@ -485,20 +485,22 @@ def test_compact_tree_counters_and_fallback_rate(name, device, hbm_scenes, dev_s
 
 
 @pytest.mark.parametrize("name", SCENES)
-@pytest.mark.parametrize("tree", ["compact", "full"])
-def test_hbm_tree_wavefront_agrees(name, tree, hbm_scenes, dev_scenes, scenes):
-    """k_wf_extend over the compact tree (MODE 2) and over the 32-byte nodes in HBM (MODE 1) trace the same paths as the
-    megakernel over the shared-memory tree."""
+@pytest.mark.parametrize("tree,sort", [("compact", 0), ("full", 0), ("compact", 1), ("full", 1)])
+def test_hbm_tree_wavefront_agrees(name, tree, sort, hbm_scenes, dev_scenes, scenes):
+    """k_wf_extend over the compact tree (MODE 2) and over the 32-byte nodes in HBM (MODE 1), with and without the rays of a
+    wave sorted by origin cell and direction octant (k_wf_keys), trace the same paths as the megakernel over the
+    shared-memory tree."""
     import os
     s = scenes[name]
     W, H, spp = SMALL[name]
     kw = dict(width=W, height=H, spp=spp, seed=11)
     a, ra, sa = dev_scenes[name].render(s.render_params(variant=1, **kw))
     os.environ["SRT_WF_TREE"] = tree
+    os.environ["SRT_WF_SORT"] = str(sort)
     try:
         b, rb, sb = hbm_scenes[name].render(s.render_params(variant=2, **kw))
     finally:
-        del os.environ["SRT_WF_TREE"]
+        del os.environ["SRT_WF_TREE"], os.environ["SRT_WF_SORT"]
     assert sa.paths == sb.paths and sa.segments == sb.segments
     fin = np.isfinite(a).all(axis=2)
     assert (np.isfinite(b).all(axis=2) == fin).all()
