@@ -79,6 +79,9 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   if (plan.variant == 2) {
     // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
     plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
+    // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
+    // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, profiles/r1_logs/ai_threads.log); below 1024 the rate falls linearly
+    if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) plan.threads = 768;
     if (const char* t = getenv("SRT_WF")) {
       int a = 0, b = 0, c = 0;
       if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
@@ -110,6 +113,8 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
     cudaFuncAttributes fa{};
     e = cudaFuncGetAttributes(&fa, plan.fn);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(dev->smem_optin - fa.sharedSizeBytes));
+    if (e == cudaSuccess && mode != 0 && getenv("SRT_WF_L1"))      // tree in HBM: ask for the largest L1 the SM can give (A/B)
+      e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(getenv("SRT_WF_L1")));
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
   } else if (plan.variant == 3) {
     // SRT_TUNE="threads,th_shade,th_leaf,th_trav" (tuning sweeps only; results do not depend on it)
@@ -135,6 +140,7 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   }
   if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(e)); }
   if (per_sm < 1) return fail(SRT_ERR_CUDA, "render kernel does not fit on an SM");
+  if (const char* b = getenv("SRT_WF_CTAS_PER_SM")) { const int k = atoi(b); if (plan.variant == 2 && k >= 1 && k < per_sm) per_sm = k; }   // A/B runs
   plan.blocks = dev->sm_count * per_sm;           // persistent grid: every CTA resident, a multiple of the SM count
 
   // work units: enough (tile, chunk) pairs per resident warp that the tail is ~1 %, chunks of >= 8 samples
