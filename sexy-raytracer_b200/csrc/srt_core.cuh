@@ -261,10 +261,23 @@ __device__ __forceinline__ int cbox_filter(const uint4& q, const RayAuxC& x, flo
   return 0;
 }
 
+#ifndef SRT_LPRIM_NO_ALLOCATE
+#define SRT_LPRIM_NO_ALLOCATE 1
+#endif
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 // one primitive of the leaf-ordered array against the ray (same decisions as tri_hit / sph_hit); `orig` = its id
 __device__ __forceinline__ bool lprim_hit(const LPrim* __restrict__ lp, unsigned u, const Ray& r, float tMin, float tCur, float& tOut,
                                           int& orig, bool& is_sphere) {
+#if SRT_LPRIM_NO_ALLOCATE
+  // a leaf's record is used once by one lane: keep it out of the L1, which the tree's hot nodes need (config 5)
+  const float4 A = ldg_stream(&lp[u].a), B = ldg_stream(&lp[u].b), C = ldg_stream(&lp[u].c), D = ldg_stream(&lp[u].d);
+#else
   const float4 A = __ldg(&lp[u].a), B = __ldg(&lp[u].b), C = __ldg(&lp[u].c), D = __ldg(&lp[u].d);
+#endif
   orig = __float_as_int(D.z);
   is_sphere = __float_as_int(D.w) != 0;
   if (is_sphere) {
