@@ -204,6 +204,8 @@ def run_b200(args):
         raise SystemExit("--gpus %d needs %d ranks (launch under torch.distributed.run); WORLD_SIZE=%d" % (args.gpus, args.gpus, world))
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG=VERSION|WARN|INFO) goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     scene, W, H, spp, depth = load_workload(args)
