@@ -204,8 +204,6 @@ def run_b200(args):
         raise SystemExit("--gpus %d needs %d ranks (launch under torch.distributed.run); WORLD_SIZE=%d" % (args.gpus, args.gpus, world))
     torch.cuda.set_device(local)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG=VERSION|WARN|INFO) goes to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     scene, W, H, spp, depth = load_workload(args)
@@ -393,7 +391,7 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 # ---- the reference arm: the reference's own CPU code, all host cores ----------------------------------------------
@@ -418,10 +416,33 @@ def run_reference(args):
             "cpu_baseline": dict(value=round(value, 4), **desc),
             "e2e": {"value": round(value, 4), "unit": "M segments/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+# stdout carries exactly ONE line, the JSON result: whatever libraries write to file descriptor 1 meanwhile (NCCL prints its
+# version banner there when NCCL_DEBUG is set) is sent to stderr, and the line itself goes to the descriptor saved here.
+_RESULT_FD = None
+
+
+def capture_stdout():
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _RESULT_FD is None:
+        sys.stdout.buffer.write(data); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 
 def main():
+    capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
