@@ -334,6 +334,8 @@ def run_b200(args):
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(args.config)
             if tr and tr.get("kernel") == kname and not args.spp and (args.config != "c5" or (args.tris, args.spheres) == (10_000_000, 100_000)):
                 traffic = tr["dram_bytes_per_launch"]
+                if tr.get("slots_in_that_launch"):        # captured on a full pool: scale to this run's average launch
+                    traffic = int(traffic * (seg / max(1, ext_launches)) / tr["slots_in_that_launch"])
         except (OSError, ValueError):
             pass
         n_l = max(1, ext_launches)

@@ -81,7 +81,9 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
     plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
     // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
     // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, profiles/r1_logs/ai_threads.log); below 1024 the rate falls linearly
-    if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) plan.threads = 768;
+    // ... and a pool of 64 Mi slots (5.4 GB + 1 GB of sort buffers): the more rays one sort orders, the smaller the region of
+    // the scene the rays in flight cover - 8 / 32 / 64 / 128 Mi slots: 63.7 / 70.3 / 71.3 / 71.1 M segments/s (r1_logs/ap_pool.log)
+    if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) { plan.threads = 768; plan.wf_slots = 1 << 26; }
     if (const char* t = getenv("SRT_WF")) {
       int a = 0, b = 0, c = 0;
       if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
