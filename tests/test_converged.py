@@ -1,0 +1,141 @@
+"""Converged-image criterion (north_star) at the sample counts BASELINE's configs name.
+
+Golden frames: oracle/make_golden_converged.py = the compiled reference rendered twice (independent mt19937 streams A, B)
+    config 3  426x240  x 1000 spp  depth 4      tests/golden/c3_masterchief_1k_image.npz   (main.cpp:176,179-180)
+    config 4  1280x720 x  256 spp  depth 4      tests/golden/c4_720p_image.npz             (main.cpp:175-181 geometry)
+    config 2  640x360  x   64 spp  depth 8      tests/golden/c2_cube_full_image.npz
+
+Stated tolerances (asserted below, quoted in DESIGN.md section 3):
+  * RGBA8 frames:  PSNR(GPU, ref_A) >= PSNR(ref_A, ref_B) - 0.5 dB  at equal spp, against A and against B;
+  * linear radiance, 16x16-tile means: the distribution of |GPU - mean(A,B)| / mean(A,B) may not be wider than the
+    reference's own |A - B| spread (quantile by quantile, factor 1.25 where 0.87 is expected for an unbiased frame),
+    and its median stays below 1 % (config 3 at 1000 spp) / 2 % (720p at 256 spp);
+  * frame totals per channel within 1e-3 + 3 |A - B|;
+  * segments per path within 0.5 % of the reference's own counter;
+  * config 4 proper (5000 spp): the GPU frame, which carries 1/20 of the noise power of a 256-spp reference frame, must
+    sit >= 2 dB ABOVE the reference's A/B floor against either reference frame (2.8 dB expected), and its tile means
+    within 0.75 x the A/B spread (0.53 expected).
+The CPU test at the end holds the plain-C port to the same golden tile means at a reduced sample count.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, psnr_u8
+
+Q = (0.5, 0.9, 0.99)
+
+
+def load(name):
+    g = np.load(os.path.join(GOLDEN, name + "_image.npz"))
+    H, W = (int(x) for x in g["shape"])
+    ok = np.unpackbits(g["finite"])[: H * W].reshape(H, W).astype(bool)
+    if "rgb_a" in g.files:
+        ra, rb = g["rgb_a"], g["rgb_b"]
+    else:
+        ra, rb = g["rgba_a"][..., :3], g["rgba_b"][..., :3]
+    return g, H, W, ok, ra, rb
+
+
+def tiles16(x, ok):
+    H, W, _ = x.shape
+    x = np.where(ok[..., None] & np.isfinite(x), x, 0)[: H // 16 * 16, : W // 16 * 16].astype(np.float64)
+    return x.reshape(H // 16, 16, W // 16, 16, 3).mean(axis=(1, 3))
+
+
+def tile_spread(t, ref, spp):
+    return np.abs(t - ref) / np.maximum(np.abs(ref), 1e-3 * spp)
+
+
+def check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp_gpu, median_cap, factor, psnr_margin):
+    spp_ref = int(g["spp"])
+    ok = ok & np.isfinite(got).all(axis=2)
+    assert ok.mean() > 0.9999
+    floor = float(g["psnr_ab"])
+    pa, pb = psnr_u8(rgba, ra, ok), psnr_u8(rgba, rb, ok)
+    assert min(pa, pb) >= floor + psnr_margin, "PSNR vs A %.2f dB, vs B %.2f dB; reference A/B floor %.2f dB" % (pa, pb, floor)
+    # segments per path against the reference's own counter
+    ref_spp = float(np.mean(g["segments"])) / (W * H * spp_ref)
+    assert abs(st.segments / st.paths - ref_spp) <= 0.005 * ref_spp
+    # linear radiance: per-sample tile means
+    ta, tb = g["tiles_a"].astype(np.float64) / spp_ref, g["tiles_b"].astype(np.float64) / spp_ref
+    tg = tiles16(got, ok) / spp_gpu
+    ref = 0.5 * (ta + tb)
+    dev_g, dev_ab = tile_spread(tg, ref, 1.0), tile_spread(ta, tb, 1.0)
+    qg, qab = np.quantile(dev_g, Q), np.quantile(dev_ab, Q)
+    assert qg[0] <= max(median_cap, 1.5 * qab[0]), "median tile deviation %.4f" % qg[0]
+    assert (qg <= factor * qab + 2e-3).all(), "tile deviation quantiles %s vs reference A/B spread %s" % (qg, qab)
+    # frame totals
+    tot_g = np.where(ok[..., None], got, 0).sum(axis=(0, 1), dtype=np.float64) / spp_gpu
+    tot_a, tot_b = g["total_a"] / spp_ref, g["total_b"] / spp_ref
+    assert (np.abs(tot_g - 0.5 * (tot_a + tot_b)) <= 1e-3 * tot_a + 3 * np.abs(tot_a - tot_b)).all(), (tot_g, tot_a, tot_b)
+    return pa, pb, floor, qg, qab
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("variant", [0, 1])
+def test_config3_1000spp_vs_reference(variant, dev_scenes, scenes):
+    g, H, W, ok, ra, rb = load("c3_masterchief_1k")
+    s = scenes["c3_masterchief"]
+    spp = int(g["spp"])
+    assert (W, H, spp, int(g["depth"])) == (426, 240, 1000, 4)
+    got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=4, seed=9, variant=variant))
+    assert st.paths == W * H * spp
+    pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.01, 1.25, -0.5)
+    print("config 3 @1000 spp variant %d: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev q50/q90/q99 %s (A/B %s)" % (st.variant, pa, pb, floor, qg, qab))
+
+
+@pytest.mark.gpu
+def test_config4_720p_256spp_vs_reference(dev_scenes, scenes):
+    g, H, W, ok, ra, rb = load("c4_720p")
+    s = scenes["c3_masterchief"]
+    spp = int(g["spp"])
+    assert (W, H, int(g["depth"])) == (1280, 720, 4)
+    got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=4, seed=9))
+    pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.02, 1.25, -0.5)
+    print("720p @%d spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (spp, pa, pb, floor, qg, qab))
+
+
+@pytest.mark.gpu
+def test_config4_5000spp_vs_reference_spread(dev_scenes, scenes):
+    """BASELINE config 4 as it is benchmarked (1280x720, 5000 spp, depth 4) against the 256-spp reference frames."""
+    g, H, W, ok, ra, rb = load("c4_720p")
+    s = scenes["c3_masterchief"]
+    got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=5000, max_bounce=4, seed=2026))
+    assert st.paths == W * H * 5000 and st.variant == 2
+    pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, 5000, 0.02, 0.75, 2.0)
+    print("720p @5000 spp: PSNR %.2f / %.2f dB vs 256-spp references, their floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
+
+
+@pytest.mark.gpu
+def test_config2_full_size_vs_reference(dev_scenes, scenes):
+    g, H, W, ok, ra, rb = load("c2_cube_full")
+    s = scenes["c2_cube"]
+    spp = int(g["spp"])
+    assert (W, H, spp, int(g["depth"])) == (640, 360, 64, 8)
+    got, rgba, st = dev_scenes["c2_cube"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=8, seed=9))
+    # a small light in a large dark room: 64 spp is far from converged (A/B floor 17.5 dB), the spread test carries the weight
+    pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.05, 1.25, -0.5)
+    print("config 2 @64 spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
+
+
+def test_port_tile_means_vs_converged_golden(scenes, port):
+    """The plain-C port (the checker that travels) against the reference's 1000-spp tile means, at 24 spp: the deviation
+    of an unbiased 24-spp frame from a 2000-spp mean is sqrt(1000/24 / 2) = 4.6 x the A/B spread; a bias would not shrink."""
+    g, H, W, ok, ra, rb = load("c3_masterchief_1k")
+    s = scenes["c3_masterchief"]
+    spp = 24
+    h = port.from_scene(s)
+    acc, st = port.render(h, s, s.render_params(width=W, height=H, spp=spp, max_bounce=4, seed=31), nthreads=8)
+    port.free(h)
+    ta, tb = g["tiles_a"].astype(np.float64) / 1000, g["tiles_b"].astype(np.float64) / 1000
+    ref = 0.5 * (ta + tb)
+    tg = tiles16(acc, ok) / spp
+    dev_g, dev_ab = tile_spread(tg, ref, 1.0), tile_spread(ta, tb, 1.0)
+    assert np.median(dev_g) <= 0.02
+    assert (np.quantile(dev_g, Q) <= 7.0 * np.quantile(dev_ab, Q) + 5e-3).all()
+    tot = np.where(ok[..., None], acc, 0).sum(axis=(0, 1), dtype=np.float64) / spp
+    assert (np.abs(tot - g["total_a"] / 1000) <= 0.01 * g["total_a"] / 1000).all()
+    ref_spp = float(np.mean(g["segments"])) / (W * H * 1000)
+    assert abs(st.segments / st.paths - ref_spp) <= 0.01 * ref_spp
