@@ -154,6 +154,9 @@ def cpu_frame_sample(args, seconds_per_core=12.0, scene=None):
         return cpu_port_sample(args, scene, seconds_per_core)
     from oracle import refbind
     kind = "reference" if refbind.RefOracle.available() else "port"
+    # load the checker in THIS process before the row-band children are forked: they inherit the mapping, and the driver's
+    # record of loaded libraries (taken in the parent) shows which implementation the reference arm ran
+    _parent_handle = refbind.RefOracle() if kind == "reference" else refbind.PortOracle()   # noqa: F841
     name, W, H, spp, depth = CONFIGS[args.config]
     cores = os.cpu_count() or 1
     seg_per_spp = W * H * 1.8
@@ -240,7 +243,7 @@ def run_b200(args):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     seg = paths = launches = ext_launches = 0
     kern_ms = ext_ms = shd_ms = 0.0
-    variant = 0
+    variant = extend_kernel = 0
     barrier()
     for a, b in ev:
         flush.fill_(1)                           # L2 flush between timed iterations, outside the event pair
@@ -252,7 +255,7 @@ def run_b200(args):
         if st is not None:
             seg += int(st.segments); paths += int(st.paths); kern_ms += st.kernel_ms
             ext_ms += st.extend_ms; shd_ms += st.shade_ms; ext_launches += st.extend_launches
-            launches += st.launches; variant = st.variant
+            launches += st.launches; variant = st.variant; extend_kernel = st.extend_kernel
         launches += 1 if rank == 0 else 0                          # k_resolve
     barrier()
     ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -265,6 +268,17 @@ def run_b200(args):
     seg_all, paths_all = tot.tolist()
     ms_all, kern_ms_max = tmax.tolist()
     value = seg_all / (ms_all * 1e-3) / 1e6
+    # the frame of the last timed step (rank 0 holds the reduced sum): CRC32 of the RGBA8 bytes + the total of the linear sums,
+    # so that runs at different GPU counts can be compared (Philox is keyed by the global sample index: the N-GPU frame equals
+    # the 1-GPU frame up to fp32 summation order - RGBA8 bytes may differ by 1 in a few pixels, the total by ~1e-6 relative)
+    frame_crc = sum_total = None
+    if rank == 0:
+        import zlib
+        frame_host = rgba.cpu().numpy()
+        frame_crc = "%08x" % (zlib.crc32(frame_host.tobytes()) & 0xffffffff)
+        sum_total = float(torch.nan_to_num(accum.double(), nan=0.0, posinf=0.0, neginf=0.0).sum().item())
+        if args.save_frame:
+            np.save(args.save_frame, frame_host.reshape(H, W, 4))
 
     # ---- e2e: host buffers through the public C-ABI calls, copies inside the timed region
     h2d = scene.host_bytes()
@@ -273,7 +287,7 @@ def run_b200(args):
     e2e_seg = 0
     barrier()
     t0 = time.perf_counter()
-    e2e_steps, e2e_kernel_ms, e2e_upload_s, e2e_close_s, e2e_scenes = [], [], [], [], []
+    e2e_steps, e2e_kernel_ms, e2e_upload_s, e2e_close_s = [], [], [], []
     for _ in range(args.steps):
         t_step = time.perf_counter()
         ds2 = dev.upload(scene)                                        # H2D: the flattened scene, every step
@@ -291,14 +305,12 @@ def run_b200(args):
             dev.set_stream(None)
         e2e_seg += int(st.segments) if st is not None else 0
         e2e_kernel_ms.append(round(float(st.kernel_ms), 1) if st is not None else None)
-        e2e_scenes.append(ds2)       # released after the timed region: srt_scene_destroy is clean-up, not part of producing a frame
+        t_close = time.perf_counter()
+        ds2.close()                  # srt_scene_destroy INSIDE the timed region: a frame's scene replica is released with it
+        e2e_close_s.append(round(time.perf_counter() - t_close, 4))
         e2e_steps.append(round(time.perf_counter() - t_step, 4))
     barrier()
     e2e_s = time.perf_counter() - t0
-    for ds2 in e2e_scenes:           # measured apart: cudaFree / cudaFreeArray of a scene took 3 ms .. 1 s on this pool's boxes
-        t_close = time.perf_counter()
-        ds2.close()
-        e2e_close_s.append(round(time.perf_counter() - t_close, 4))
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     se = torch.tensor([float(e2e_seg)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -308,69 +320,101 @@ def run_b200(args):
 
     line = None
     if rank == 0:
-        # ---- roofline of the dominant kernel (k_render_mega): counters from a short counted pass of the same frame
+        # ---- roofline of the dominant kernel.  Per-segment work of the REFERENCE algorithm (B box tests, Lt / Ls
+        # triangle / sphere leaf tests) is counted by a short pass of the same frame through an exact-walk kernel (the flat
+        # megakernel when the tree is in shared memory: same Philox keys, same paths, node visits = the reference's recursion).
+        in_smem = scene.nodes.nbytes + 32 <= 227 * 1024
         dev.set_counters(True)
         stc = ds.render_accumulate(accum.data_ptr(), scene.render_params(width=W, height=H, spp=spp, max_bounce=depth,
                                                                          sample_begin=0, sample_count=max(1, min(8, spp)), seed=2026,
-                                                                         variant=variant))
+                                                                         variant=1 if in_smem else variant))
         c = dev.last_counters()
         dev.set_counters(False)
         bps_all, k = algorithmic_bytes_per_segment(c, int(stc.segments), n_maps=0 if args.config == "c5" else 2)
-        # the traversal kernel's part of SURVEY 8(d)'s figure: node + primitive fetches + the ray; the accept-time UV and
-        # texel bytes belong to the shade kernel
+        # the traversal kernel's part of SURVEY 8(d)'s figures: node + primitive fetches + the ray / box + leaf tests; the
+        # accept-time UV and texel bytes and the shading flops belong to the shade kernel
         bps = 32 * k["B"] + 36 * k["Lt"] + 40 * k["Ls"] + 28
-        kname = {1: "k_render_mega", 2: "k_wf_extend", 3: "k_render_phased"}.get(variant, "?")
-        in_smem = scene.nodes.nbytes + 32 <= 227 * 1024
-        note = ("algorithmic bytes are node/primitive/ray fetches of the traversal kernel; for this scene the nodes are served "
-                "from shared memory (whole BVH staged per CTA) and primitives from L1/L2, so DRAM traffic is far below "
-                "them and frac may exceed what HBM alone could deliver - see profiles/ and DESIGN.md 'Rooflines'") if in_smem else (
-                "tree in HBM: every lane reads one unpredictable 32-byte sector per step; the measured ceiling of the B200 for that "
-                "pattern is 40-50 G sectors/s (1.3-1.6 TB/s) beyond the L2 (tools/rand_access_bench.cu, profiles/r1_rand_access_b200.txt), "
-                "not the streaming peak - the walk over the compact 16-byte tree fetches fewer bytes than the algorithmic 32 per node")
+        fl_seg = 27 * k["B"] + 65 * k["Lt"] + 25 * k["Ls"]
+        kname = {1: "k_render_mega", 2: "k_wf_extend2" if extend_kernel else "k_wf_extend", 3: "k_render_phased"}.get(variant, "?")
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
-        # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel in this workload's launch shape,
-        # from the committed `ncu --set full` capture (profiles/r1_traffic.json names the report it was read from)
-        traffic = None
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(args.config)
-            if tr and tr.get("kernel") == kname and not args.spp and (args.config != "c5" or (args.tris, args.spheres) == (10_000_000, 100_000)):
-                traffic = tr["dram_bytes_per_launch"]
-                if tr.get("slots_in_that_launch"):        # captured on a full pool: scale to this run's average launch
-                    traffic = int(traffic * (seg / max(1, ext_launches)) / tr["slots_in_that_launch"])
-        except (OSError, ValueError):
-            pass
         n_l = max(1, ext_launches)
         seg_rank0 = seg / n_l                                  # rank 0's segments (= rays traced) per launch of the dominant kernel
         launch_s = ext_ms / n_l * 1e-3                         # its average launch duration, CUDA events inside the timed region
-        achieved = bps * seg_rank0 / launch_s / 1e9
-        fl_seg = 27 * k["B"] + 65 * k["Lt"] + 25 * k["Ls"]     # traversal kernel's part of SURVEY 8(d)'s flop figure
+        # counters of ONE launch of the dominant kernel in this workload's launch shape from the committed ncu captures
+        # (profiles/r2_ncu_summary.json names the report each number was read from; r1_traffic.json for kernels unchanged since)
+        ncu = None
+        full_size = not args.spp and (args.config != "c5" or (args.tris, args.spheres) == (10_000_000, 100_000))
+        for fname in ("r2_ncu_summary.json", "r1_traffic.json"):
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", fname))).get(args.config)
+            except (OSError, ValueError):
+                continue
+            if tr and tr.get("kernel") == kname and tr.get("node_bytes", extend_kernel) == extend_kernel and full_size:
+                ncu = dict(tr, file="profiles/" + fname)
+                break
+        traffic = None
+        if ncu:
+            traffic = ncu["dram_bytes_per_launch"]
+            if ncu.get("slots_in_that_launch"):               # captured on a full pool: scale to this run's average launch
+                traffic = int(traffic * seg_rank0 / ncu["slots_in_that_launch"])
+        alg_gbs = bps * seg_rank0 / launch_s / 1e9
         fl = fl_seg * seg_rank0 / launch_s / 1e12
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-        fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
-        roofline = {"kernel": kname, "bound": "hbm", "achieved": round(achieved, 1), "peak": peak_hbm,
-                    "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback", "unit": "GB/s",
-                    "frac": round(achieved / peak_hbm, 4), "traffic": traffic,
-                    "bytes_per_segment": round(bps, 1), "bytes_per_segment_whole_path": round(bps_all, 1),
-                    "per_segment": {a: round(b, 3) for a, b in k.items()},
-                    "segments_per_launch": round(seg_rank0, 1), "launch_ms": round(launch_s * 1e3, 4),
-                    "launches_per_step": round(n_l / max(1, args.steps), 1),
-                    "share_of_step": {kname: round(ext_ms / max(kern_ms, 1e-9), 4), "k_wf_shade": round(shd_ms / max(kern_ms, 1e-9), 4)},
-                    "note": note,
-                    "fp32": {"achieved_tflops": round(fl, 3), "peak_nominal_tflops": round(fp32_peak, 1),
-                             "frac_fma_peak": round(fl / fp32_peak, 4), "frac_unfused_peak": round(fl / (fp32_peak / 2), 4),
-                             "flops_per_segment": round(fl_seg, 1)}}
+        fp32_nominal = 148 * 128 * 2 * sm_max * 1e6 / 1e12
+        unfused_peak, unfused_src = fp32_nominal / 2, "nominal FFMA peak / 2 (148 SMs x 128 lanes x sm_max_mhz)"
         try:   # the un-fused mul + add ceiling measured on this pool's B200 (tools/fp32_peak.cu)
-            mp = json.load(open(os.path.join(ROOT, "profiles", "r1_fp32_peak_b200.json")))
-            roofline["fp32"]["peak_measured_unfused_tflops"] = mp["unfused_mul_add_tflops"]
-            roofline["fp32"]["peak_measured_ffma_tflops"] = mp["ffma_tflops"]
-            roofline["fp32"]["frac_measured_unfused_peak"] = round(fl / mp["unfused_mul_add_tflops"], 4)
+            mp_ = json.load(open(os.path.join(ROOT, "profiles", "r1_fp32_peak_b200.json")))
+            unfused_peak, unfused_src = float(mp_["unfused_mul_add_tflops"]), "measured (tools/fp32_peak.cu, profiles/r1_fp32_peak_b200.json)"
         except (OSError, ValueError, KeyError):
             pass
+        common = {"kernel": kname, "traffic": traffic,
+                  "per_segment": {a: round(b, 3) for a, b in k.items()}, "flops_per_segment": round(fl_seg, 1),
+                  "bytes_per_segment": round(bps, 1), "bytes_per_segment_whole_path": round(bps_all, 1),
+                  "segments_per_launch": round(seg_rank0, 1), "launch_ms": round(launch_s * 1e3, 4),
+                  "launches_per_step": round(n_l / max(1, args.steps), 1),
+                  "share_of_step": {kname: round(ext_ms / max(kern_ms, 1e-9), 4), "k_wf_shade2": round(shd_ms / max(kern_ms, 1e-9), 4)},
+                  "algorithmic_gbs": round(alg_gbs, 1),
+                  "dram_gbs_measured": round(traffic / launch_s / 1e9, 1) if traffic else None,
+                  "frac_streaming": round(traffic / launch_s / 1e9 / peak_hbm, 4) if traffic else None,
+                  "traffic_over_algorithmic": round(traffic / (bps * seg_rank0), 4) if traffic else None,
+                  "hbm_peak_gbs": peak_hbm, "ncu": {x: ncu[x] for x in ncu if x not in ("dram_bytes_per_launch", "slots_in_that_launch")} if ncu else None}
+        if in_smem:
+            # tree in shared memory: HBM sees only the ray slots of the wave; the kernel is bound by instruction issue / the FP32 and
+            # ALU pipes.  Roof = un-fused fp32 (the reference's arithmetic may not contract to FMA): algorithmic flops of the
+            # reference's traversal per second against the measured un-fused mul+add ceiling.
+            roofline = dict(common, bound="fp32_unfused", achieved=round(fl, 3), peak=round(unfused_peak, 2), peak_source=unfused_src,
+                            unit="TFLOP/s", frac=round(fl / unfused_peak, 4),
+                            note="algorithmic flops = 27 B + 65 Lt + 25 Ls per segment (SURVEY 8.4) with B, Lt, Ls of the reference's "
+                                 "ordered traversal counted on this frame; k_wf_extend2 reaches the same leaves through a conservative "
+                                 "walk (FFMA slab test on outward-rounded boxes), so it executes fewer operations than it is credited with")
+        else:
+            # tree in HBM / L2: every step of a lane is one unpredictable 32-byte sector; the roof is the random-sector rate of the
+            # memory system at this footprint (tools/rand_access_bench.cu), not the streaming peak
+            foot = float(scene.nodes.nbytes) / 2 + 64.0 * scene.n_prim       # the compact tree (16 B / node) + leaf-ordered primitives
+            peak_sec, src = 43.4, "fallback: 1 GB footprint row of profiles/r1_rand_access_b200.txt"
+            try:
+                rows = []
+                for ln in open(os.path.join(ROOT, "profiles", "r1_rand_access_b200.txt")):
+                    f = ln.split()
+                    if len(f) >= 7 and f[1] == "MB" and f[2] == "32" and f[3] == "1":
+                        rows.append((float(f[0]) * 1048576.0, float(f[5])))
+                fit = [r for r in rows if r[0] >= foot] or rows[-1:]
+                peak_sec, src = fit[0][1], "measured random 32-byte sector rate at a %d MB footprint (profiles/r1_rand_access_b200.txt)" % (fit[0][0] / 1048576)
+            except (OSError, ValueError, IndexError):
+                pass
+            sectors = (traffic if traffic else bps * seg_rank0) / 32.0 / launch_s / 1e9
+            roofline = dict(common, bound="hbm_random_sector", achieved=round(sectors, 2), peak=peak_sec, peak_source=src, unit="G sectors/s",
+                            frac=round(sectors / peak_sec, 4), footprint_bytes=int(foot),
+                            achieved_source="measured DRAM bytes / 32" if traffic else "ALGORITHMIC bytes / 32 (no ncu capture of this workload shape)",
+                            fp32_unfused_frac=round(fl / unfused_peak, 4),
+                            note="the walk over the compact 16-byte tree with sorted rays is served partly by the L2 (hit rate ~74 %): DRAM sectors "
+                                 "per second are what the HBM delivers, against the measured random-sector ceiling at this footprint; "
+                                 "frac_streaming = the same bytes against the streaming peak")
         cpu = None
         if world == 1 and not args.no_cpu:
             v, desc = cpu_frame_sample(args, scene=scene)
@@ -390,10 +434,10 @@ def run_b200(args):
                 "render_kernel_ms_per_step": round(kern_ms_max / args.steps, 3),
                 "e2e": {"value": round(e2e_value, 2), "unit": "M segments/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "s_per_step": round(te.item() / args.steps, 4), "s_steps_rank0": e2e_steps,
-                        "upload_s_steps_rank0": e2e_upload_s, "kernel_ms_steps_rank0": e2e_kernel_ms, "scene_destroy_s_after_timing_rank0": e2e_close_s,
-                        "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out)" if world == 1 else
-                                "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H"},
-                "gpu_launches": launches, "variant": variant, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}
+                        "upload_s_steps_rank0": e2e_upload_s, "kernel_ms_steps_rank0": e2e_kernel_ms, "scene_destroy_s_steps_rank0": e2e_close_s,
+                        "path": "srt_scene_create(host SoA) + srt_render(host RGBA8 out) + srt_scene_destroy" if world == 1 else
+                                "srt_scene_create(host SoA) + srt_render_accumulate + NCCL reduce + srt_resolve + D2H + srt_scene_destroy"},
+                "gpu_launches": launches, "variant": variant, "frame_crc": frame_crc, "sum_total": sum_total, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu}
     ds.close()
     dev.close()
     if world > 1:
@@ -463,6 +507,7 @@ def main():
     ap.add_argument("--tris", type=int, default=10_000_000, help="config c5: triangles")
     ap.add_argument("--spheres", type=int, default=100_000, help="config c5: spheres")
     ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 flat megakernel, 2 wavefront, 3 phased megakernel")
+    ap.add_argument("--save-frame", default="", help="rank 0 writes the RGBA8 frame of the last timed step to this .npy file")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

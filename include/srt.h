@@ -174,7 +174,7 @@ typedef struct srt_render_params {
   int32_t  spp;            /* numSamples of the whole frame (main.cpp:178): the divisor of resolve */
   int32_t  sample_begin;   /* this call renders global samples [sample_begin, sample_begin+sample_count) */
   int32_t  sample_count;   /* of every pixel (spp split across GPUs); 0 = all spp      */
-  int32_t  max_bounce;     /* main.cpp:180                                                       */
+  int32_t  max_bounce;     /* main.cpp:180; 0 = every path is black and no segment is traced (main.cpp:36-37) */
   float    background[3];  /* main.cpp:170                                                       */
   uint64_t seed;           /* Philox key                                                         */
   int32_t  rr_begin;       /* Russian roulette from this bounce on; 0 = off (the reference has none) */
@@ -199,6 +199,8 @@ typedef struct srt_stats {
   float    shade_ms;
   int32_t  extend_launches;
   int32_t  variant;        /* the variant that ran: 1 flat megakernel, 2 wavefront, 3 phased megakernel */
+  int32_t  extend_kernel;  /* variant 2: 0 = k_wf_extend (exact ordered walk), 16 / 32 = k_wf_extend2 with 16- / 32-byte nodes */
+  int32_t  reserved0;
 } srt_stats;
 
 typedef struct srt_device srt_device;
@@ -215,6 +217,10 @@ int64_t     srt_scene_device_bytes(const srt_scene* scene);
 /* ---- parity gate: hittableList::hit on explicit rays (hittablelist.h:33-47 -> bvh.h:97-105) -- */
 srt_status  srt_trace_rays(srt_scene* scene, const srt_ray* rays, int64_t n, float t_min, float t_max,
                            srt_hit* out_hits);
+
+/* the same rays through the PRODUCTION extend kernel of the wavefront renderer (variant 2) in the launch shape, tree layout and
+ * ray ordering it uses for this scene - one wave over n pool slots; returns the primitive id (-1 = miss) and t bits per ray  */
+srt_status  srt_trace_rays_wavefront(srt_scene* scene, const srt_ray* rays, int64_t n, int32_t* out_prim, float* out_t);
 
 /* ---- one frame: replaces glDevice::rtFrame + the loop main.cpp:200-227 ------------------------
  * out_sum_rgb  (optional) [H*W*3] float: sum over this call's samples of rayColor, row 0 = top
@@ -262,6 +268,14 @@ srt_status  srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* 
 srt_status  srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_render_params* params,
                              const int32_t* pixel_xy /*n*2*/, const int32_t* sample /*n*/, int64_t n,
                              srt_ray* out_rays);
+
+/* aabb::hit (aabb.h:11-27) through the device's box predicates, one (ray, box, tMin, tMax) row per decision:
+ * boxes[n*6] = min3 max3, tminmax[n*2].  predicate 0 = filtered predicate of the exact walks (with its fallback), 1 = 16-bit snapped
+ * box filter of the compact tree (with its fallback): out_decision must equal aabb::hit; out_path (optional) = 1 where the
+ * reference's own arithmetic ran.  predicate 2 / 3 = the conservative cull of k_wf_extend2 on 32- / 16-byte nodes (tMin is the
+ * walk's constant 0.001): 1 = kept, 0 = culled - never 0 where aabb::hit is true; out_path = 1 where the ray takes the exact walk */
+srt_status  srt_aabb_kat(srt_device* dev, const srt_ray* rays, const float* boxes, const float* tminmax, int64_t n,
+                         int32_t predicate, int32_t* out_decision, int32_t* out_path);
 
 /* ---- misc ----------------------------------------------------------------------------------- */
 int         srt_abi_version(void);

@@ -73,7 +73,8 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("segments", C.c_uint64), ("node_visits", C.c_uint64),
                 ("leaf_tests", C.c_uint64), ("kernel_ms", C.c_float), ("launches", C.c_int32),
-                ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("extend_launches", C.c_int32), ("variant", C.c_int32)]
+                ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("extend_launches", C.c_int32), ("variant", C.c_int32),
+                ("extend_kernel", C.c_int32), ("reserved0", C.c_int32)]
 
 
 # numpy dtypes with the same layout (for bulk arrays of rays / hits / nodes)
@@ -96,6 +97,8 @@ PROTOTYPES = {
     "srt_scene_destroy": (None, [_vp]),
     "srt_scene_device_bytes": (C.c_int64, [_vp]),
     "srt_trace_rays": (C.c_int, [_vp, _vp, C.c_int64, C.c_float, C.c_float, _vp]),
+    "srt_trace_rays_wavefront": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp]),
+    "srt_aabb_kat": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int32, _vp, _vp]),
     "srt_render": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.POINTER(Stats)]),
     "srt_render_accumulate": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, C.POINTER(Stats)]),
     "srt_resolve": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_int32, _vp]),

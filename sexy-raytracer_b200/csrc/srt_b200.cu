@@ -14,6 +14,7 @@
 #include "srt_kernels.cuh"
 #include "srt_phased.cuh"
 #include "srt_wavefront.cuh"
+#include "srt_extend2.cuh"
 
 using namespace srt;
 
@@ -290,7 +291,34 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     s->root_hi[0] = r0.lo.w; s->root_hi[1] = r0.hi.x; s->root_hi[2] = r0.hi.y;
   }
   s->nodes_in_smem = s->node_bytes > 0 && s->node_bytes <= dev->smem_optin;
-  if (const char* f = getenv("SRT_FORCE_GLOBAL_TREE")) if (atoi(f)) s->nodes_in_smem = 0;   // tests: small scenes through the HBM paths
+  {  // k_wf_extend2's preconditions (srt_extend2.cuh): nested boxes, no box-less primitives, coordinates within 2^40
+    bool ok = filter_ok && n_real > 0;
+    for (int64_t i = 0; ok && i < d->n_nodes; i++) {
+      const srt_bvh_node& p = d->nodes[i];
+      const bool leaf = p.left < 0 && (p.right == SRT_BVH_NONE || p.right < 0);
+      if (leaf) continue;
+      for (int32_t c : {p.left, p.right}) {
+        if (c < 0) { ok = false; break; }            // a primitive hanging directly under an inner node (NODE_NO_BOX)
+        const srt_bvh_node& q = d->nodes[c];
+        for (int k = 0; k < 3; k++) if (!(q.bmin[k] >= p.bmin[k]) || !(q.bmax[k] <= p.bmax[k])) ok = false;
+      }
+    }
+    s->sc.x2_ok = ok ? 1 : 0;
+    std::vector<float> cx[3];
+    for (int i = 0; i < n_real; i++) {
+      int32_t w7; memcpy(&w7, &nodes[i].hi.w, 4);
+      if (w7 == NODE_INNER || w7 == NODE_NO_BOX) continue;
+      cx[0].push_back(0.5f * (nodes[i].lo.x + nodes[i].lo.w)); cx[1].push_back(0.5f * (nodes[i].lo.y + nodes[i].hi.x));
+      cx[2].push_back(0.5f * (nodes[i].lo.z + nodes[i].hi.y));
+    }
+    for (int k = 0; k < 3; k++) {
+      float c = 0.0f;
+      if (!cx[k].empty()) { std::nth_element(cx[k].begin(), cx[k].begin() + cx[k].size() / 2, cx[k].end()); c = cx[k][cx[k].size() / 2]; }
+      s->sc.x2_centre[k] = std::isfinite(c) ? c : 0.0f;
+    }
+  }
+  if (const char* t = getenv("SRT_DEBUG_TUNING")) if (!strcmp(t, "1"))
+    if (const char* f = getenv("SRT_FORCE_GLOBAL_TREE")) if (atoi(f)) s->nodes_in_smem = 0;   // tests: small scenes through the HBM paths
 
   // compact tree + leaf-ordered primitives for trees that stay in HBM (srt_core.cuh)
   std::vector<int32_t> lp_src;            // leaf order -> original primitive id

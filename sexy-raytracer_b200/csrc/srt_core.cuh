@@ -115,6 +115,11 @@ struct Scene {
   const Mat*   mats;   int n_mat;
   const Tex*   texs;   int n_tex;
   int filter_ok;       // every box coordinate is finite and small enough for the filtered predicate
+  // k_wf_extend2 (srt_extend2.cuh): the tree is nested (every node's box contains its children's), has no box-less
+  // primitives and coordinates within 2^40 -> inner nodes may be culled conservatively; centre = the point box
+  // coordinates are taken relative to in the walk's 16-byte nodes (median of the leaf boxes' centres)
+  int x2_ok;
+  float x2_centre[3];
 };
 
 // ---- aabb::hit, aabb.h:11-27 --------------------------------------------------------------------

@@ -27,10 +27,34 @@ static srt_status ensure_grid(srt_device* dev, int begin, int count, RenderArgs&
   return SRT_OK;
 }
 
+// Tuning overrides (launch shapes, tree modes) are read from the environment ONLY when SRT_DEBUG_TUNING=1: a stray variable
+// must not change a production launch.  They exist for A/B measurements and for tests that push small scenes through the
+// large-scene paths; results never depend on them.
+//   SRT_WF="slots,threads,th_walk"   SRT_WF_TREE=full|compact   SRT_WF_SORT=0|1   SRT_WF_KEY=0|1   SRT_WF_SHADE=1|2
+//   SRT_WF_X2=0|16|32 (k_wf_extend2 off / 16-byte / 32-byte nodes)   SRT_WF_L1=<carve-out %>   SRT_WF_CTAS_PER_SM=<k>
+//   SRT_TUNE="threads,th_shade,th_leaf,th_trav" (variant 3)   SRT_FORCE_GLOBAL_TREE=1 (srt_scene_create)
+static const char* tune_env(const char* name) {
+  const char* on = getenv("SRT_DEBUG_TUNING");
+  if (!on || strcmp(on, "1") != 0) return nullptr;
+  return getenv(name);
+}
+
 struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
   int wf_slots, wf_th_walk, wf_shade_chunk; const void* wf_shade;     // variant 2
+  int x2_fmt, x2_park;                                                // variant 2 with k_wf_extend2: node bytes (0 = k_wf_extend), entries per warp
 };
+
+typedef void (*extend2_fn)(Scene, WfPool, WfCursors*, int, int, unsigned long long*);
+template <int THREADS>
+extend2_fn pick_extend2(bool count, int fmt) {
+  if (count) return fmt == 16 ? k_wf_extend2<true, 16, THREADS> : k_wf_extend2<true, 32, THREADS>;
+  return fmt == 16 ? k_wf_extend2<false, 16, THREADS> : k_wf_extend2<false, 32, THREADS>;
+}
+// shared memory of k_wf_extend2: the staged nodes + `park` 16-byte entries per warp
+static size_t x2_smem_bytes(int n_nodes, int fmt, int threads, int park) {
+  return (size_t)n_nodes * (size_t)fmt + (size_t)(threads / 32) * (size_t)park * 16;
+}
 
 typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
 template <int THREADS>
@@ -45,6 +69,79 @@ template <int THREADS>
 phased_fn pick_phased(bool count, bool smem) {
   if (count) return smem ? k_render_phased<true, true, THREADS> : k_render_phased<true, false, THREADS>;
   return smem ? k_render_phased<false, true, THREADS> : k_render_phased<false, false, THREADS>;
+}
+
+// variant 2: the launch shape of the EXTEND and SHADE kernels for this scene (`total` = paths of the call)
+static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& plan, int& per_sm) {
+  srt_device* dev = s->dev;
+  cudaError_t e;
+  plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
+  // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
+  plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
+  // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
+  // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, profiles/r1_logs/ai_threads.log); below 1024 the rate falls linearly
+  // ... and a pool of 64 Mi slots (5.4 GB + 1 GB of sort buffers): the more rays one sort orders, the smaller the region of
+  // the scene the rays in flight cover - 8 / 32 / 64 / 128 Mi slots: 63.7 / 70.3 / 71.3 / 71.1 M segments/s (r1_logs/ap_pool.log)
+  if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) { plan.threads = 768; plan.wf_slots = 1 << 26; }
+  bool wf_env = false;
+  if (const char* t = tune_env("SRT_WF")) {
+    int a = 0, b = 0, c = 0;
+    if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
+      plan.wf_slots = a; plan.threads = b; plan.wf_th_walk = c; wf_env = true;
+    }
+  }
+    if ((long long)plan.wf_slots > total) plan.wf_slots = (int)((total + 255) / 256 * 256);
+  // Trees in HBM: the compact tree pays off once the 32-byte nodes no longer fit the L2 (config 5: 378 MB of nodes,
+  // 47.6 vs 36.7 M segments/s); an L2-resident tree is faster through its full nodes (1 M triangles: 236 vs 221).
+  // SRT_WF_TREE=full|compact overrides (A/B measurements, tests).
+  const char* tree = tune_env("SRT_WF_TREE");
+  bool compact = s->sc.cnodes && s->node_bytes > dev->l2_bytes;
+  if (tree && !strcmp(tree, "full")) compact = false;
+  if (tree && !strcmp(tree, "compact")) compact = s->sc.cnodes != nullptr;
+  const int mode = s->nodes_in_smem ? 0 : compact ? 2 : 1;
+  // Tree in shared memory: k_wf_extend2 (conservative walk + parked leaf tests, srt_extend2.cuh) whenever the scene allows
+  // it and its nodes + park lists fit; 16-byte nodes first (half the shared-memory wavefronts per step), 32-byte otherwise.
+  plan.x2_fmt = 0; plan.x2_park = 64;
+  if (mode == 0 && s->sc.x2_ok) {
+    int want = SRT_X2_DEFAULT_FMT;
+    if (const char* e = tune_env("SRT_WF_X2")) want = atoi(e);
+    cudaFuncAttributes fa2{};
+    for (int fmt : {want, want == 16 ? 32 : 0}) {
+      if (fmt != 16 && fmt != 32) continue;
+      if (fmt == 16 && s->sc.n_nodes > 32000) continue;                     // 16-bit links
+      const void* f2 = plan.threads == 1024 ? (const void*)pick_extend2<1024>(dev->counters, fmt)
+                       : plan.threads == 768 ? (const void*)pick_extend2<768>(dev->counters, fmt)
+                       : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
+                                             : (const void*)pick_extend2<512>(dev->counters, fmt);
+      if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
+      const size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, plan.x2_park);
+      if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
+      plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
+      if (!wf_env) plan.wf_th_walk = SRT_X2_DEFAULT_TH;
+      break;
+    }
+  }
+  if (!plan.x2_fmt) {
+    extend_fn fn = plan.threads == 1024 ? pick_extend<1024>(dev->counters, mode)
+                   : plan.threads == 768 ? pick_extend<768>(dev->counters, mode)
+                   : plan.threads == 256 ? pick_extend<256>(dev->counters, mode)
+                                         : pick_extend<512>(dev->counters, mode);
+    plan.fn = (const void*)fn;
+  }
+  {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
+    const char* sh = tune_env("SRT_WF_SHADE");
+    const bool sorted = !(sh && atoi(sh) == 1);
+    plan.wf_shade_chunk = sorted ? 512 : 256;
+    plan.wf_shade = sorted ? (dev->counters ? (const void*)k_wf_shade2<true> : (const void*)k_wf_shade2<false>)
+                           : (dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>);
+  }
+  cudaFuncAttributes fa{};
+  e = cudaFuncGetAttributes(&fa, plan.fn);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(dev->smem_optin - fa.sharedSizeBytes));
+  if (e == cudaSuccess && mode != 0 && tune_env("SRT_WF_L1"))      // tree in HBM: ask for the largest L1 the SM can give (A/B)
+    e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(tune_env("SRT_WF_L1")));
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
+  return e;
 }
 
 srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_params* P, RenderPlan& plan) {
@@ -77,50 +174,10 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   int per_sm = 0;
   cudaError_t e;
   if (plan.variant == 2) {
-    // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
-    plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
-    // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
-    // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, profiles/r1_logs/ai_threads.log); below 1024 the rate falls linearly
-    // ... and a pool of 64 Mi slots (5.4 GB + 1 GB of sort buffers): the more rays one sort orders, the smaller the region of
-    // the scene the rays in flight cover - 8 / 32 / 64 / 128 Mi slots: 63.7 / 70.3 / 71.3 / 71.1 M segments/s (r1_logs/ap_pool.log)
-    if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) { plan.threads = 768; plan.wf_slots = 1 << 26; }
-    if (const char* t = getenv("SRT_WF")) {
-      int a = 0, b = 0, c = 0;
-      if (sscanf(t, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1024 && (b == 256 || b == 512 || b == 768 || b == 1024) && c >= 1) {
-        plan.wf_slots = a; plan.threads = b; plan.wf_th_walk = c;
-      }
-    }
-    const long long total = (long long)A.n_tiles * 32 * A.sample_count;
-    if ((long long)plan.wf_slots > total) plan.wf_slots = (int)((total + 255) / 256 * 256);
-    // Trees in HBM: the compact tree pays off once the 32-byte nodes no longer fit the L2 (config 5: 378 MB of nodes,
-    // 47.6 vs 36.7 M segments/s); an L2-resident tree is faster through its full nodes (1 M triangles: 236 vs 221).
-    // SRT_WF_TREE=full|compact overrides (A/B measurements, tests).
-    const char* tree = getenv("SRT_WF_TREE");
-    bool compact = s->sc.cnodes && s->node_bytes > dev->l2_bytes;
-    if (tree && !strcmp(tree, "full")) compact = false;
-    if (tree && !strcmp(tree, "compact")) compact = s->sc.cnodes != nullptr;
-    const int mode = s->nodes_in_smem ? 0 : compact ? 2 : 1;
-    extend_fn fn = plan.threads == 1024 ? pick_extend<1024>(dev->counters, mode)
-                   : plan.threads == 768 ? pick_extend<768>(dev->counters, mode)
-                   : plan.threads == 256 ? pick_extend<256>(dev->counters, mode)
-                                         : pick_extend<512>(dev->counters, mode);
-    plan.fn = (const void*)fn;
-    {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
-      const char* sh = getenv("SRT_WF_SHADE");
-      const bool sorted = !(sh && atoi(sh) == 1);
-      plan.wf_shade_chunk = sorted ? 512 : 256;
-      plan.wf_shade = sorted ? (dev->counters ? (const void*)k_wf_shade2<true> : (const void*)k_wf_shade2<false>)
-                             : (dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>);
-    }
-    cudaFuncAttributes fa{};
-    e = cudaFuncGetAttributes(&fa, plan.fn);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(dev->smem_optin - fa.sharedSizeBytes));
-    if (e == cudaSuccess && mode != 0 && getenv("SRT_WF_L1"))      // tree in HBM: ask for the largest L1 the SM can give (A/B)
-      e = cudaFuncSetAttribute(plan.fn, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(getenv("SRT_WF_L1")));
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, plan.fn, plan.threads, plan.smem);
+    e = plan_wavefront(s, (long long)A.n_tiles * 32 * A.sample_count, plan, per_sm);
   } else if (plan.variant == 3) {
     // SRT_TUNE="threads,th_shade,th_leaf,th_trav" (tuning sweeps only; results do not depend on it)
-    if (const char* t = getenv("SRT_TUNE")) {
+    if (const char* t = tune_env("SRT_TUNE")) {
       int a = 0, b = 0, c = 0, d = 0;
       if (sscanf(t, "%d,%d,%d,%d", &a, &b, &c, &d) == 4 && (a == 256 || a == 512 || a == 768 || a == 1024) && b >= 1 && c >= 1 && d >= 1) {
         plan.threads = a; plan.tune = PhaseTune{b, c, d};
@@ -142,7 +199,7 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
   }
   if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(e)); }
   if (per_sm < 1) return fail(SRT_ERR_CUDA, "render kernel does not fit on an SM");
-  if (const char* b = getenv("SRT_WF_CTAS_PER_SM")) { const int k = atoi(b); if (plan.variant == 2 && k >= 1 && k < per_sm) per_sm = k; }   // A/B runs
+  if (const char* b = tune_env("SRT_WF_CTAS_PER_SM")) { const int k = atoi(b); if (plan.variant == 2 && k >= 1 && k < per_sm) per_sm = k; }   // A/B runs
   plan.blocks = dev->sm_count * per_sm;           // persistent grid: every CTA resident, a multiple of the SM count
 
   // work units: enough (tile, chunk) pairs per resident warp that the tail is ~1 %, chunks of >= 8 samples
@@ -192,9 +249,9 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   }
   // ray ordering (srt_wavefront.cuh: k_wf_keys) for trees in HBM; SRT_WF_SORT=0|1 overrides (A/B runs)
   bool sort_rays = !s->nodes_in_smem && s->node_bytes > dev->l2_bytes;
-  if (const char* e = getenv("SRT_WF_SORT")) sort_rays = atoi(e) != 0;
+  if (const char* e = tune_env("SRT_WF_SORT")) sort_rays = atoi(e) != 0;
   WfSortGrid grid{};
-  if (const char* e = getenv("SRT_WF_KEY")) grid.mode = atoi(e);
+  if (const char* e = tune_env("SRT_WF_KEY")) grid.mode = atoi(e);
   unsigned *keys_in = nullptr, *keys_out = nullptr, *vals_in = nullptr, *vals_out = nullptr;
   if (sort_rays) {
     if (dev->sort_cap < N) {
@@ -220,7 +277,10 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   Scene sc = s->sc; RenderArgs A = plan.A; WfCursors* cur = dev->d_wf_cur; unsigned long long* ctr = dev->d_counters;
   int th_walk = plan.wf_th_walk;
   void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
-  void* extend_args[] = {&sc, &pool, &cur, &th_walk, &ctr};
+  int x2_park = plan.x2_park;
+  void* extend_args_v1[] = {&sc, &pool, &cur, &th_walk, &ctr};
+  void* extend_args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
+  void** extend_args = plan.x2_fmt ? extend_args_x2 : extend_args_v1;
   const unsigned reset_blocks = (unsigned)((N + 255) / 256);
   unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS;   // persistent: resident CTAs per SM x two rounds
   {
@@ -283,13 +343,21 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     stats->kernel_ms = ms; stats->launches = launches;
     for (long long w = timed; w < waves; w++) CK(collect(w));     // the last LAG+1 waves (the stream is idle now)
     stats->extend_ms = (float)extend_ms; stats->shade_ms = (float)shade_ms;
-    stats->extend_launches = (int)waves; stats->variant = 2;
+    stats->extend_launches = (int)waves; stats->variant = 2; stats->extend_kernel = plan.x2_fmt;
   }
   return SRT_OK;
 }
 
 srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
   srt_device* dev = s->dev;
+  if (plan.A.max_bounce <= 0) {     // rayColor returns (0,0,0) before world.hit (main.cpp:36-37): nothing to add, no segment traced
+    if (stats) {
+      memset(stats, 0, sizeof *stats);
+      stats->paths = (uint64_t)plan.A.W * plan.A.H * (uint64_t)plan.A.sample_count;
+      stats->variant = plan.variant;
+    }
+    return SRT_OK;
+  }
   if (plan.variant == 2) return run_wavefront(s, plan, accum_dev, stats);
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaEventRecord(dev->ev0, dev->stream));
@@ -395,6 +463,102 @@ srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_
   }
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(out_hits, dh.p, (size_t)n * sizeof(srt_hit), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  return SRT_OK;
+}
+
+// hittableList::hit for explicit rays through the PRODUCTION extend kernel of the wavefront (the launch shape, tree mode and
+// ray ordering plan_wavefront picks for this scene): rays are loaded into pool slots, one EXTEND wave runs, (prim, t) come back.
+srt_status srt_trace_rays_wavefront(srt_scene* s, const srt_ray* rays, int64_t n, int32_t* out_prim, float* out_t) {
+  if (!s || n < 0 || (n > 0 && (!rays || !out_prim || !out_t))) return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  if (n > (int64_t)1 << 30) return fail(SRT_ERR_UNSUPPORTED, "too many rays for one wave");
+  srt_device* dev = s->dev;
+  CK(cudaSetDevice(dev->gpu));
+  RenderPlan plan;
+  int per_sm = 0;
+  cudaError_t e = plan_wavefront(s, (long long)n, plan, per_sm);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_CUDA, std::string("occupancy query: ") + cudaGetErrorString(e)); }
+  if (per_sm < 1) return fail(SRT_ERR_CUDA, "extend kernel does not fit on an SM");
+  if (const char* b = tune_env("SRT_WF_CTAS_PER_SM")) { const int k = atoi(b); if (k >= 1 && k < per_sm) per_sm = k; }
+  const int blocks = dev->sm_count * per_sm;
+  DevBuf dr, dro, drd, dh, dcur, dsort, dtmp;
+  CK(dr.alloc((size_t)n * sizeof(srt_ray)));
+  CK(dro.alloc((size_t)n * sizeof(float4))); CK(drd.alloc((size_t)n * sizeof(float4))); CK(dh.alloc((size_t)n * sizeof(int2)));
+  CK(dcur.alloc(sizeof(WfCursors)));
+  CK(cudaMemcpyAsync(dr.p, rays, (size_t)n * sizeof(srt_ray), cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemsetAsync(dcur.p, 0, sizeof(WfCursors), dev->stream));
+  CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
+  WfPool pool{};
+  pool.ray_o = dro.as<float4>(); pool.ray_d = drd.as<float4>(); pool.hit = dh.as<int2>(); pool.n_slots = (int)n; pool.order = nullptr;
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_wf_load_rays<<<nb, 256, 0, dev->stream>>>(dr.as<srt_ray>(), (long long)n, pool);
+  bool sort_rays = !s->nodes_in_smem && s->node_bytes > dev->l2_bytes;
+  if (const char* ev = tune_env("SRT_WF_SORT")) sort_rays = atoi(ev) != 0;
+  if (sort_rays) {
+    WfSortGrid grid{};
+    for (int k = 0; k < 3; k++) {
+      const float lo = s->root_lo[k], ext = s->root_hi[k] - s->root_lo[k];
+      grid.org[k] = lo; grid.inv_cell[k] = ext > 0 ? 256.0f / ext : 0.0f;
+    }
+    CK(dsort.alloc(4 * (size_t)n * sizeof(unsigned)));
+    unsigned *keys_in = dsort.as<unsigned>(), *keys_out = keys_in + n, *vals_in = keys_out + n, *vals_out = vals_in + n;
+    size_t tmp = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const unsigned*)nullptr, (unsigned*)nullptr, (const unsigned*)nullptr, (unsigned*)nullptr,
+                                       (int)n, 0, 28, dev->stream));
+    CK(dtmp.alloc(tmp));
+    k_wf_keys<<<nb, 256, 0, dev->stream>>>(pool, grid, keys_in, vals_in);
+    CK(cub::DeviceRadixSort::SortPairs(dtmp.p, tmp, (const unsigned*)keys_in, keys_out, (const unsigned*)vals_in, vals_out, (int)n, 0, 28, dev->stream));
+    pool.order = vals_out;
+  }
+  Scene sc = s->sc; WfCursors* cur = dcur.as<WfCursors>(); unsigned long long* ctr = dev->d_counters;
+  int th_walk = plan.wf_th_walk, x2_park = plan.x2_park;
+  void* args_v1[] = {&sc, &pool, &cur, &th_walk, &ctr};
+  void* args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
+  CK(cudaLaunchKernel(plan.fn, dim3(blocks), dim3(plan.threads), plan.x2_fmt ? args_x2 : args_v1, plan.smem, dev->stream));
+  std::vector<int2> h((size_t)n);
+  CK(cudaMemcpyAsync(h.data(), dh.p, (size_t)n * sizeof(int2), cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  for (int64_t i = 0; i < n; i++) { out_prim[i] = h[i].x; memcpy(&out_t[i], &h[i].y, 4); }
+  return SRT_OK;
+}
+
+// aabb::hit (aabb.h:11-27) decisions of the device's box predicates on explicit (ray, box, tMin, tMax) rows - see k_aabb_kat.
+// boxes[n*6] = min3 max3; tminmax[n*2]; out_path optional.  Predicates 2 and 3 (the conservative cull of k_wf_extend2) use the
+// walk's constant tMin = 0.001 and return 1 = kept / 0 = culled: a row the reference HITS must never come back 0.
+srt_status srt_aabb_kat(srt_device* dev, const srt_ray* rays, const float* boxes, const float* tminmax, int64_t n, int32_t predicate,
+                        int32_t* out_decision, int32_t* out_path) {
+  if (!dev || n < 0 || predicate < 0 || predicate > 3 || (n > 0 && (!rays || !boxes || !tminmax || !out_decision)))
+    return fail(SRT_ERR_INVALID, "bad argument");
+  if (n == 0) return SRT_OK;
+  CK(cudaSetDevice(dev->gpu));
+  KatGrid g{};
+  {   // the 16-bit grid over the union of the boxes (predicate 1) and the centre of the walk's coordinates (2, 3)
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int64_t i = 0; i < n; i++) for (int k = 0; k < 3; k++) {
+      const float a = boxes[6 * i + k], b = boxes[6 * i + 3 + k];
+      if (std::isfinite(a) && a < lo[k]) lo[k] = a;
+      if (std::isfinite(b) && b > hi[k]) hi[k] = b;
+    }
+    for (int k = 0; k < 3; k++) {
+      if (!(hi[k] >= lo[k])) { lo[k] = 0; hi[k] = 1; }
+      float c = (float)((hi[k] - lo[k]) / 65534.0);
+      c = std::nextafter(std::max(c, 1e-30f), std::numeric_limits<float>::infinity());
+      g.org[k] = (float)lo[k]; if ((double)g.org[k] > lo[k]) g.org[k] = std::nextafter(g.org[k], -std::numeric_limits<float>::infinity());
+      g.cell[k] = c;
+      g.centre[k] = (float)(0.5 * (lo[k] + hi[k]));
+    }
+  }
+  DevBuf dr, db, dt, dd, dp;
+  CK(dr.alloc((size_t)n * sizeof(srt_ray))); CK(db.alloc((size_t)n * 24)); CK(dt.alloc((size_t)n * 8)); CK(dd.alloc((size_t)n * 4)); CK(dp.alloc((size_t)n * 4));
+  CK(cudaMemcpyAsync(dr.p, rays, (size_t)n * sizeof(srt_ray), cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemcpyAsync(db.p, boxes, (size_t)n * 24, cudaMemcpyHostToDevice, dev->stream));
+  CK(cudaMemcpyAsync(dt.p, tminmax, (size_t)n * 8, cudaMemcpyHostToDevice, dev->stream));
+  k_aabb_kat<<<(unsigned)((n + 127) / 128), 128, 0, dev->stream>>>(dr.as<srt_ray>(), db.as<float>(), dt.as<float>(), (long long)n, predicate, g,
+                                                                  dd.as<int>(), dp.as<int>());
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out_decision, dd.p, (size_t)n * 4, cudaMemcpyDeviceToHost, dev->stream));
+  if (out_path) CK(cudaMemcpyAsync(out_path, dp.p, (size_t)n * 4, cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
 }

@@ -74,6 +74,15 @@ class Device:
     def resolve_dev(self, sum_dev_ptr, W, H, spp, rgba_dev_ptr):
         _check(lib().srt_resolve(self.h, sum_dev_ptr, W, H, spp, rgba_dev_ptr))
 
+    def aabb_kat(self, rays, boxes, tminmax, predicate=0):
+        """-> (decision [n] i32, path [n] i32); see srt_aabb_kat in include/srt.h"""
+        rays = np.ascontiguousarray(rays, abi.RAY_DTYPE)
+        boxes = np.ascontiguousarray(boxes, np.float32).reshape(-1, 6)
+        tmm = np.ascontiguousarray(tminmax, np.float32).reshape(-1, 2)
+        dec, path = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.int32)
+        _check(lib().srt_aabb_kat(self.h, _ptr(rays), _ptr(boxes), _ptr(tmm), len(rays), predicate, _ptr(dec), _ptr(path)))
+        return dec, path
+
     def getray_kat(self, camera, inp):
         inp = np.ascontiguousarray(inp, np.float32).reshape(-1, 5)
         out = np.zeros(len(inp), abi.RAY_DTYPE)
@@ -112,6 +121,13 @@ class DeviceScene:
         hits = np.zeros(len(rays), abi.HIT_DTYPE)
         _check(lib().srt_trace_rays(self.h, _ptr(rays), len(rays), t_min, t_max, _ptr(hits)))
         return hits
+
+    def trace_wavefront(self, rays):
+        """srt_trace_rays_wavefront: one production EXTEND wave over explicit rays -> (prim [n] i32, t [n] f32)"""
+        rays = np.ascontiguousarray(rays, abi.RAY_DTYPE)
+        prim, t = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.float32)
+        _check(lib().srt_trace_rays_wavefront(self.h, _ptr(rays), len(rays), _ptr(prim), _ptr(t)))
+        return prim, t
 
     def render(self, params=None, want_sum=True, want_rgba=True, camera=None):
         """srt_render with host buffers -> (sum [H,W,3] f32 | None, rgba [H,W,4] u8 | None, Stats)"""

@@ -11,6 +11,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from sexy_raytracer_b200.scene import Scene  # noqa: E402
 
+# the tests push small scenes through the large-scene code paths with the library's tuning overrides (srt_launch.cuh: tune_env)
+os.environ["SRT_DEBUG_TUNING"] = "1"
+
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 SCENES = ["c1_shirley", "c2_cube", "c3_masterchief", "c3s_globe"]
 

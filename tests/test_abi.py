@@ -47,7 +47,7 @@ def test_struct_sizes_match_header():
     assert C.sizeof(abi.BvhNode) == 32 and abi.NODE_DTYPE.itemsize == 32
     assert C.sizeof(abi.Ray) == 28 and C.sizeof(abi.Camera) == 24 * 4
     assert C.sizeof(abi.Hit) == abi.HIT_DTYPE.itemsize == 4 * 4 + 12 * 4 + 2 * 4
-    assert C.sizeof(abi.Stats) == 4 * 8 + 6 * 4
+    assert C.sizeof(abi.Stats) == 4 * 8 + 8 * 4
 
 
 def test_no_cpu_fallback(lib):

@@ -213,3 +213,12 @@ def test_reference_from_desc_equals_native(ref, scenes):
     assert ref.trace(a, rays).tobytes() == ref.trace(b, rays).tobytes()
     ref.free(a)
     ref.free(b)
+
+
+def test_port_aabb_adversarial_vs_reference(port, ref):
+    """aabb::hit on the generated threshold set (rayset.aabb_adversarial) that the GPU predicates are held to: the C port's
+    decisions equal the compiled reference's, so the GPU box can use the port as the checker for this set."""
+    import rayset
+    for seed in (11, 12, 13):
+        rays, boxes, tmm = rayset.aabb_adversarial(300000, seed)
+        assert (port.aabb_kat(rays, boxes, tmm) == ref.aabb_kat(rays, boxes, tmm)).all()
