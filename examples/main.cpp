@@ -6,7 +6,7 @@
 // (writeColorTarget + stbi_write_png) becomes the device's resolve + srt_png_write.
 //
 //   g++ -std=c++17 -Iinclude examples/main.cpp -Lsexy-raytracer_b200 -lsrt_host -o sexy-raytracer
-//   SRT_B200_LIBRARY=sexy-raytracer_b200/libsrt_b200.so ./sexy-raytracer [data dir | shirley] [height] [samples] [out.png] [passes]
+//   SRT_B200_LIBRARY=sexy-raytracer_b200/libsrt_b200.so ./sexy-raytracer [data dir | shirley] [height] [samples] [out.png] [passes] [seed]
 // passes > 1 renders progressively (the reference's `while (glDevice.rtFrame(...))` loop, main.cpp:195-199): samples/passes
 // more samples per pixel per pass into a film on the device, a checkpoint <out.png>.srtf after every pass; an existing
 // checkpoint of the same size is resumed.
@@ -57,10 +57,12 @@ int main(int argc, char** argv) {
     std::cerr << "device: " << device.lastError() << "\n";
     return 1;
   }
+  std::cerr << "rendering on " << device.gpuCount() << " GPU(s)\n";
   srt_stats stats;
   const int passes = argc > 5 ? atoi(argv[5]) : 1;
+  const uint64_t seed = argc > 6 ? strtoull(argv[6], nullptr, 10) : 1;
   if (passes <= 1) {
-    if (!device.rtFrame(target, imageWidth, imageHeight, mainCamera, background, numSamples, maxBounce, 1, &stats)) {   // main.cpp:197-227
+    if (!device.rtFrame(target, imageWidth, imageHeight, mainCamera, background, numSamples, maxBounce, seed, &stats)) {   // main.cpp:197-227
       std::cerr << "device: " << device.lastError() << "\n";
       return 1;
     }
@@ -70,7 +72,7 @@ int main(int argc, char** argv) {
       std::cerr << "resuming " << ckpt << " at " << device.samplesDone() << " samples per pixel\n";
     while (device.samplesDone() < numSamples) {                 // while (glDevice.rtFrame(...))  main.cpp:195-199
       const int k = std::min((numSamples + passes - 1) / passes, numSamples - device.samplesDone());
-      if (!device.rtFrameProgressive(target, imageWidth, imageHeight, mainCamera, background, k, maxBounce, 1, &stats) ||
+      if (!device.rtFrameProgressive(target, imageWidth, imageHeight, mainCamera, background, k, maxBounce, seed, &stats) ||
           !device.saveCheckpoint(ckpt.c_str())) {
         std::cerr << "device: " << device.lastError() << "\n";
         return 1;

@@ -178,6 +178,9 @@ typedef struct srt_render_params {
   float    background[3];  /* main.cpp:170                                                       */
   uint64_t seed;           /* Philox key                                                         */
   int32_t  rr_begin;       /* Russian roulette from this bounce on; 0 = off (the reference has none) */
+  /* variant 2 adds every finished path to its pixel with red.global.add.f32: the order of a pixel's samples depends on the
+     schedule, so two runs of the same frame agree to fp32 summation order (~1e-6 relative, RGBA8 within 1), not bit for bit;
+     variants 1 and 3 sum a pixel's samples in index order and are bit-reproducible.                                      */
   int32_t  variant;        /* 0 = auto (wavefront for frames of >= 4 Mi paths over trees of >= 256 nodes, else megakernel),
                               1 = flat megakernel, 2 = wavefront, 3 = phased megakernel         */
   int32_t  sampler;        /* where in the pixel a sample lies: 0 = random jitter (main.cpp:210-211, the live code),
@@ -236,6 +239,28 @@ srt_status  srt_render_accumulate(srt_scene* scene, const srt_camera* cam, const
                                   float* accum_dev, srt_stats* stats);
 srt_status  srt_resolve(srt_device* dev, const float* sum_dev, int32_t width, int32_t height, int32_t spp,
                         uint8_t* rgba8_dev);
+
+/* ---- several GPUs behind one handle: glDevice::init / rtFrame (gl.h:28-31, main.cpp:190-199) for a whole box ---------------
+ * A device group owns one srt_device per GPU.  srt_scene_group_create uploads a replica of the flattened scene to each of them
+ * (in parallel); srt_render_group splits the samples of every pixel across the GPUs (the remainder to the first ones - the
+ * Philox stream is keyed by the global sample index, so the frame does not depend on the split, up to fp32 summation order),
+ * renders on all of them at once (one host thread per GPU), sums the per-GPU fp32 radiance buffers on the first GPU (peer
+ * copies over NVLink + one add per peer: the frame's only exchange) and resolves there.  Outputs and statistics are those of
+ * srt_render; kernel_ms is the slowest GPU's.  gpu_ids = NULL with n_gpus = 0 takes every visible GPU; an id may repeat (two
+ * devices sharing one GPU - of use for tests on a single-GPU box).  Multi-process callers (one process per GPU, NCCL) use
+ * srt_render_accumulate + their own reduce + srt_resolve instead.                                                        */
+typedef struct srt_device_group srt_device_group;
+typedef struct srt_scene_group  srt_scene_group;
+srt_status  srt_device_group_create(const int* gpu_ids, int n_gpus, srt_device_group** out);
+void        srt_device_group_destroy(srt_device_group* group);
+int32_t     srt_device_group_size(const srt_device_group* group);
+srt_device* srt_device_group_device(srt_device_group* group, int32_t k);      /* borrowed: counters, streams */
+srt_status  srt_scene_group_create(srt_device_group* group, const srt_scene_desc* desc, srt_scene_group** out);
+void        srt_scene_group_destroy(srt_scene_group* scenes);
+srt_scene*  srt_scene_group_scene(srt_scene_group* scenes, int32_t k);         /* borrowed */
+srt_status  srt_sample_split(int32_t begin, int32_t count, int32_t n, int32_t k, int32_t* out_begin, int32_t* out_count);
+srt_status  srt_render_group(srt_scene_group* scenes, const srt_camera* cam, const srt_render_params* params,
+                             float* out_sum_rgb, uint8_t* out_rgba8, srt_stats* stats);
 
 /* ---- progressive accumulation: glDevice::rtFrame as a per-frame loop (main.cpp:195-199, gl.h:269-320), headless ----
  * A film is a persistent fp32 sum buffer on the device + the number of samples per pixel it holds.  add_samples

@@ -56,12 +56,19 @@ srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, c
 void       srt_host_free(void* p);
 
 /* ---- checkpoint of a progressive render: the fp32 sum buffer + how many samples per pixel it holds.
- * File: "SRTF" u32 version=1, i32 width, height, samples_done, u64 seed, then width*height*3 little-endian floats.   */
+ * File: "SRTF" u32 version (1; write2: 2), i32 width, height, samples_done, u64 seed, then width*height*3 little-endian floats.   */
 srt_status srt_checkpoint_write(const char* path, int32_t width, int32_t height, int32_t samples_done, uint64_t seed,
                                 const float* sum_rgb);
 /* *out_sum_rgb is malloc'ed (free with srt_host_free) */
 srt_status srt_checkpoint_read(const char* path, int32_t* width, int32_t* height, int32_t* samples_done, uint64_t* seed,
                                float** out_sum_rgb);
+/* version 2 of the file: i32 sampler, i32 max_bounce follow the seed, so that a resume with other parameters (which would mix
+ * two sample streams under continuing global sample indices) can be refused.  read2 also reads version 1 (-1 = not recorded);
+ * out_sampler / out_max_bounce may be NULL.                                                                            */
+srt_status srt_checkpoint_write2(const char* path, int32_t width, int32_t height, int32_t samples_done, uint64_t seed,
+                                 int32_t sampler, int32_t max_bounce, const float* sum_rgb);
+srt_status srt_checkpoint_read2(const char* path, int32_t* width, int32_t* height, int32_t* samples_done, uint64_t* seed,
+                                int32_t* out_sampler, int32_t* out_max_bounce, float** out_sum_rgb);
 
 /* ---- whole scenes through the C++ host classes of srt_world.hpp (for callers that are not C++: tests, bench) ----------
  * which: 1 = the Shirley sphere block of main.cpp:92-122 re-enabled (+ main.cpp:124-131,143-144)   [BASELINE config 1]

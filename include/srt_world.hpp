@@ -299,7 +299,11 @@ class flatScene {
 class b200Device {
  public:
   ~b200Device() { terminate(); }
-  bool init(int w, int h, const hittableList& world, int gpu = 0, const char* library_path = nullptr);
+  // gpu < 0 (the default): every visible GPU - the samples of every pixel are split across them and summed on the first one
+  // (srt_render_group, include/srt.h); gpu >= 0: that GPU alone; or an explicit list.
+  bool init(int w, int h, const hittableList& world, int gpu = -1, const char* library_path = nullptr);
+  bool init(int w, int h, const hittableList& world, const std::vector<int>& gpus, const char* library_path = nullptr);
+  int  gpuCount() const;
   bool rtFrame(void* frameData, int w, int h, const camera& cam, const color3f& background, int numSamples, int maxBounce,
                uint64_t seed = 1, srt_stats* stats = nullptr);
   // Progressive form - what the reference's `while (glDevice.rtFrame(...))` loop is for (main.cpp:195-199): each call adds
@@ -307,7 +311,10 @@ class b200Device {
   // saveCheckpoint / loadCheckpoint write / restore the film (fp32 sums + sample count) so a long render can resume.
   bool rtFrameProgressive(void* frameData, int w, int h, const camera& cam, const color3f& background, int samples, int maxBounce,
                           uint64_t seed = 1, srt_stats* stats = nullptr);
+  // A film holds ONE sample stream: once it has samples, a call with another seed, sampler or maxBounce is refused (it would
+  // continue the global sample indices with different draws); resetFilm() starts over.
   int  samplesDone() const;
+  void resetFilm();
   bool saveCheckpoint(const char* path);
   bool loadCheckpoint(const char* path, int w, int h);
   void terminate();
@@ -317,11 +324,14 @@ class b200Device {
   int sampler = 0;
  private:
   void* so = nullptr;
-  srt_device* dev = nullptr;
-  srt_scene* scene = nullptr;
+  srt_device_group* group = nullptr;
+  srt_scene_group* scenes = nullptr;
+  srt_device* dev = nullptr;          // borrowed from the group: its first GPU
+  srt_scene* scene = nullptr;         // borrowed: the replica on that GPU
   srt_film* film = nullptr;
   int film_w = 0, film_h = 0;
   uint64_t film_seed = 1;
+  int film_sampler = -1, film_bounce = -1;      // -1: not known (a version-1 checkpoint)
   std::string err;
 };
 

@@ -102,6 +102,15 @@ PROTOTYPES = {
     "srt_render": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.POINTER(Stats)]),
     "srt_render_accumulate": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, C.POINTER(Stats)]),
     "srt_resolve": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_int32, _vp]),
+    "srt_device_group_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
+    "srt_device_group_destroy": (None, [_vp]),
+    "srt_device_group_size": (C.c_int32, [_vp]),
+    "srt_device_group_device": (_vp, [_vp, C.c_int32]),
+    "srt_scene_group_create": (C.c_int, [_vp, C.POINTER(SceneDesc), C.POINTER(_vp)]),
+    "srt_scene_group_destroy": (None, [_vp]),
+    "srt_scene_group_scene": (_vp, [_vp, C.c_int32]),
+    "srt_sample_split": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "srt_render_group": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.POINTER(Stats)]),
     "srt_film_create": (C.c_int, [_vp, C.c_int32, C.c_int32, C.POINTER(_vp)]),
     "srt_film_destroy": (None, [_vp]),
     "srt_film_add_samples": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(RenderParams), C.c_int32, C.POINTER(Stats)]),

@@ -82,7 +82,7 @@ const char* srt_status_string(srt_status s) {
   }
 }
 
-srt_status srt_device_create(int gpu_id, srt_device** out) {
+srt_status srt_device_create(int gpu_id, srt_device** out) try {
   if (!out) return fail(SRT_ERR_INVALID, "out is NULL");
   *out = nullptr;
   int n = 0;
@@ -103,7 +103,7 @@ srt_status srt_device_create(int gpu_id, srt_device** out) {
   CK(cudaMalloc(&d->d_counters, 8 * sizeof(unsigned long long)));
   *out = d;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 void srt_device_destroy(srt_device* d) {
   if (!d) return;
@@ -125,17 +125,17 @@ void srt_device_destroy(srt_device* d) {
   delete d;
 }
 
-srt_status srt_set_counters(srt_device* d, int enabled) {
+srt_status srt_set_counters(srt_device* d, int enabled) try {
   if (!d) return fail(SRT_ERR_INVALID, "device is NULL");
   d->counters = enabled ? 1 : 0;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 void* srt_device_stream(srt_device* d) { return d ? (void*)d->stream : nullptr; }
-srt_status srt_device_set_stream(srt_device* d, void* cuda_stream) {
+srt_status srt_device_set_stream(srt_device* d, void* cuda_stream) try {
   if (!d) return fail(SRT_ERR_INVALID, "device is NULL");
   d->stream = cuda_stream ? (cudaStream_t)cuda_stream : d->own_stream;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 }  // extern "C"
 
@@ -241,7 +241,7 @@ void srt_scene_destroy(srt_scene* s) {
 
 int64_t srt_scene_device_bytes(const srt_scene* s) { return s ? s->bytes : 0; }
 
-srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene** out) {
+srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene** out) try {
   if (!dev || !d || !out) return fail(SRT_ERR_INVALID, "NULL argument");
   *out = nullptr;
   if (d->n_tri < 0 || d->n_sph < 0 || d->n_nodes < 0 || d->n_mat < 0 || d->n_tex < 0) return fail(SRT_ERR_INVALID, "negative count");
@@ -489,8 +489,9 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   }
   *out = s;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 }  // extern "C"
 
 #include "srt_launch.cuh"
+#include "srt_group.cuh"

@@ -389,16 +389,16 @@ srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, sr
 extern "C" {
 
 srt_status srt_render_accumulate(srt_scene* s, const srt_camera* cam, const srt_render_params* P, float* accum_dev,
-                                 srt_stats* stats) {
+                                 srt_stats* stats) try {
   if (!accum_dev) return fail(SRT_ERR_INVALID, "accum_dev is NULL");
   RenderPlan plan;
   srt_status rc = plan_render(s, cam, P, plan);
   if (rc) return rc;
   CK(cudaSetDevice(s->dev->gpu));
   return run_render(s, plan, accum_dev, stats);
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_resolve(srt_device* dev, const float* sum_dev, int32_t W, int32_t H, int32_t spp, uint8_t* rgba8_dev) {
+srt_status srt_resolve(srt_device* dev, const float* sum_dev, int32_t W, int32_t H, int32_t spp, uint8_t* rgba8_dev) try {
   if (!dev || !sum_dev || !rgba8_dev || W <= 0 || H <= 0 || spp <= 0) return fail(SRT_ERR_INVALID, "bad argument");
   CK(cudaSetDevice(dev->gpu));
   int n = W * H;
@@ -406,10 +406,10 @@ srt_status srt_resolve(srt_device* dev, const float* sum_dev, int32_t W, int32_t
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 srt_status srt_render(srt_scene* s, const srt_camera* cam, const srt_render_params* P, float* out_sum_rgb,
-                      uint8_t* out_rgba8, srt_stats* stats) {
+                      uint8_t* out_rgba8, srt_stats* stats) try {
   RenderPlan plan;
   srt_status rc = plan_render(s, cam, P, plan);
   if (rc) return rc;
@@ -438,9 +438,9 @@ srt_status srt_render(srt_scene* s, const srt_camera* cam, const srt_render_para
   if (out_sum_rgb) CK(cudaMemcpyAsync(out_sum_rgb, acc, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_min, float t_max, srt_hit* out_hits) {
+srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_min, float t_max, srt_hit* out_hits) try {
   if (!s || n < 0 || (n > 0 && (!rays || !out_hits))) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   srt_device* dev = s->dev;
@@ -465,11 +465,11 @@ srt_status srt_trace_rays(srt_scene* s, const srt_ray* rays, int64_t n, float t_
   CK(cudaMemcpyAsync(out_hits, dh.p, (size_t)n * sizeof(srt_hit), cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 // hittableList::hit for explicit rays through the PRODUCTION extend kernel of the wavefront (the launch shape, tree mode and
 // ray ordering plan_wavefront picks for this scene): rays are loaded into pool slots, one EXTEND wave runs, (prim, t) come back.
-srt_status srt_trace_rays_wavefront(srt_scene* s, const srt_ray* rays, int64_t n, int32_t* out_prim, float* out_t) {
+srt_status srt_trace_rays_wavefront(srt_scene* s, const srt_ray* rays, int64_t n, int32_t* out_prim, float* out_t) try {
   if (!s || n < 0 || (n > 0 && (!rays || !out_prim || !out_t))) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   if (n > (int64_t)1 << 30) return fail(SRT_ERR_UNSUPPORTED, "too many rays for one wave");
@@ -521,13 +521,13 @@ srt_status srt_trace_rays_wavefront(srt_scene* s, const srt_ray* rays, int64_t n
   CK(cudaStreamSynchronize(dev->stream));
   for (int64_t i = 0; i < n; i++) { out_prim[i] = h[i].x; memcpy(&out_t[i], &h[i].y, 4); }
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 // aabb::hit (aabb.h:11-27) decisions of the device's box predicates on explicit (ray, box, tMin, tMax) rows - see k_aabb_kat.
 // boxes[n*6] = min3 max3; tminmax[n*2]; out_path optional.  Predicates 2 and 3 (the conservative cull of k_wf_extend2) use the
 // walk's constant tMin = 0.001 and return 1 = kept / 0 = culled: a row the reference HITS must never come back 0.
 srt_status srt_aabb_kat(srt_device* dev, const srt_ray* rays, const float* boxes, const float* tminmax, int64_t n, int32_t predicate,
-                        int32_t* out_decision, int32_t* out_path) {
+                        int32_t* out_decision, int32_t* out_path) try {
   if (!dev || n < 0 || predicate < 0 || predicate > 3 || (n > 0 && (!rays || !boxes || !tminmax || !out_decision)))
     return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
@@ -561,11 +561,11 @@ srt_status srt_aabb_kat(srt_device* dev, const srt_ray* rays, const float* boxes
   if (out_path) CK(cudaMemcpyAsync(out_path, dp.p, (size_t)n * 4, cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 // counters of the last srt_trace_rays or render call (only with srt_set_counters(dev, 1)):
 // node visits, leaf tests, exact (unfiltered) box tests, sphere leaf tests, segments ending on a triangle
-srt_status srt_last_counters(srt_device* dev, uint64_t* out5) {
+srt_status srt_last_counters(srt_device* dev, uint64_t* out5) try {
   uint64_t* out3 = out5;
   if (!dev || !out5) return fail(SRT_ERR_INVALID, "NULL argument");
   unsigned long long h[8];
@@ -573,10 +573,10 @@ srt_status srt_last_counters(srt_device* dev, uint64_t* out5) {
   CK(cudaMemcpy(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost));
   out3[0] = h[2]; out3[1] = h[3]; out3[2] = h[4]; out3[3] = h[6]; out3[4] = h[7];
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 srt_status srt_shade_kat(srt_scene* s, const srt_ray* rays_in, const srt_hit* hits, const float* xi, int64_t n,
-                         float* out_att, float* out_emit, srt_ray* out_rays, int32_t* out_scattered) {
+                         float* out_att, float* out_emit, srt_ray* out_rays, int32_t* out_scattered) try {
   if (!s || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   for (int64_t i = 0; i < n; i++) if (hits[i].mat < 0 || hits[i].mat >= s->sc.n_mat) return fail(SRT_ERR_INVALID, "hit material id out of range");
@@ -597,9 +597,9 @@ srt_status srt_shade_kat(srt_scene* s, const srt_ray* rays_in, const srt_hit* hi
   CK(cudaMemcpyAsync(out_scattered, ds.p, n * 4, cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_texture_kat(srt_scene* s, int32_t tex, const float* uvp, int64_t n, float* out_rgb) {
+srt_status srt_texture_kat(srt_scene* s, int32_t tex, const float* uvp, int64_t n, float* out_rgb) try {
   if (!s || n < 0 || tex < 0 || tex >= s->sc.n_tex) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   srt_device* dev = s->dev;
@@ -612,9 +612,9 @@ srt_status srt_texture_kat(srt_scene* s, int32_t tex, const float* uvp, int64_t 
   CK(cudaMemcpyAsync(out_rgb, dout.p, n * 12, cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* in, int64_t n, srt_ray* out_rays) {
+srt_status srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* in, int64_t n, srt_ray* out_rays) try {
   if (!dev || !cam || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   CK(cudaSetDevice(dev->gpu));
@@ -626,10 +626,10 @@ srt_status srt_getray_kat(srt_device* dev, const srt_camera* cam, const float* i
   CK(cudaMemcpyAsync(out_rays, dout.p, n * sizeof(srt_ray), cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 srt_status srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_render_params* P, const int32_t* pixel_xy,
-                            const int32_t* sample, int64_t n, srt_ray* out_rays) {
+                            const int32_t* sample, int64_t n, srt_ray* out_rays) try {
   if (!dev || !cam || !P || n < 0) return fail(SRT_ERR_INVALID, "bad argument");
   if (n == 0) return SRT_OK;
   CK(cudaSetDevice(dev->gpu));
@@ -650,7 +650,7 @@ srt_status srt_primary_rays(srt_device* dev, const srt_camera* cam, const srt_re
   CK(cudaMemcpyAsync(out_rays, dout.p, n * sizeof(srt_ray), cudaMemcpyDeviceToHost, dev->stream));
   CK(cudaStreamSynchronize(dev->stream));
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 }  // extern "C"
 
@@ -664,7 +664,7 @@ struct srt_film {
 
 extern "C" {
 
-srt_status srt_film_create(srt_device* dev, int32_t W, int32_t H, srt_film** out) {
+srt_status srt_film_create(srt_device* dev, int32_t W, int32_t H, srt_film** out) try {
   if (!dev || !out || W <= 0 || H <= 0) return fail(SRT_ERR_INVALID, "bad argument");
   *out = nullptr;
   CK(cudaSetDevice(dev->gpu));
@@ -678,7 +678,7 @@ srt_status srt_film_create(srt_device* dev, int32_t W, int32_t H, srt_film** out
   if (e != cudaSuccess) { cudaGetLastError(); cudaFree(f->sum); delete f; return fail(SRT_ERR_CUDA, cudaGetErrorString(e)); }
   *out = f;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 void srt_film_destroy(srt_film* f) {
   if (!f) return;
@@ -690,7 +690,7 @@ void srt_film_destroy(srt_film* f) {
 int32_t srt_film_samples(const srt_film* f) { return f ? f->done : 0; }
 
 srt_status srt_film_add_samples(srt_film* f, srt_scene* s, const srt_camera* cam, const srt_render_params* P, int32_t count,
-                                srt_stats* stats) {
+                                srt_stats* stats) try {
   if (!f || !s || !P || count <= 0) return fail(SRT_ERR_INVALID, "bad argument");
   if (s->dev != f->dev) return fail(SRT_ERR_INVALID, "film and scene live on different devices");
   if (P->width != f->W || P->height != f->H) return fail(SRT_ERR_INVALID, "render size differs from the film's");
@@ -701,9 +701,9 @@ srt_status srt_film_add_samples(srt_film* f, srt_scene* s, const srt_camera* cam
   if (rc) return rc;
   f->done += count;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_film_resolve(srt_film* f, uint8_t* out_rgba8, float* out_sum_rgb) {
+srt_status srt_film_resolve(srt_film* f, uint8_t* out_rgba8, float* out_sum_rgb) try {
   if (!f) return fail(SRT_ERR_INVALID, "film is NULL");
   if (f->done <= 0) return fail(SRT_ERR_INVALID, "no samples accumulated yet");
   srt_device* dev = f->dev;
@@ -722,15 +722,15 @@ srt_status srt_film_resolve(srt_film* f, uint8_t* out_rgba8, float* out_sum_rgb)
     CK(cudaStreamSynchronize(dev->stream));
   }
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_film_load(srt_film* f, const float* sum_rgb, int32_t samples_done) {
+srt_status srt_film_load(srt_film* f, const float* sum_rgb, int32_t samples_done) try {
   if (!f || !sum_rgb || samples_done < 0) return fail(SRT_ERR_INVALID, "bad argument");
   CK(cudaSetDevice(f->dev->gpu));
   CK(cudaMemcpyAsync(f->sum, sum_rgb, (size_t)f->W * f->H * 3 * sizeof(float), cudaMemcpyHostToDevice, f->dev->stream));
   CK(cudaStreamSynchronize(f->dev->stream));
   f->done = samples_done;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 }  // extern "C"

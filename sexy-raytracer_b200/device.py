@@ -165,6 +165,55 @@ class DeviceScene:
         return out
 
 
+class DeviceGroup:
+    """srt_device_group: several GPUs behind one handle (gpu_ids=None: every visible GPU)."""
+
+    def __init__(self, gpu_ids=None):
+        self.h = C.c_void_p()
+        if gpu_ids is None:
+            _check(lib().srt_device_group_create(None, 0, C.byref(self.h)))
+        else:
+            ids = (C.c_int * len(gpu_ids))(*gpu_ids)
+            _check(lib().srt_device_group_create(ids, len(gpu_ids), C.byref(self.h)))
+
+    def __len__(self):
+        return int(lib().srt_device_group_size(self.h))
+
+    def close(self):
+        if self.h:
+            lib().srt_device_group_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def upload(self, scene):
+        return SceneGroup(self, scene)
+
+
+class SceneGroup:
+    """srt_scene_group: one replica of a flattened scene per GPU of the group."""
+
+    def __init__(self, group, scene):
+        self.group, self.scene = group, scene
+        self.h = C.c_void_p()
+        d = scene.desc()
+        _check(lib().srt_scene_group_create(group.h, C.byref(d), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().srt_scene_group_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def render(self, params=None, want_sum=True, want_rgba=True, camera=None):
+        """srt_render_group -> (sum | None, rgba | None, Stats)"""
+        P = params if params is not None else self.scene.render_params()
+        cam = camera if camera is not None else self.scene.camera_struct()
+        acc = np.zeros((P.height, P.width, 3), np.float32) if want_sum else None
+        rgba = np.zeros((P.height, P.width, 4), np.uint8) if want_rgba else None
+        st = abi.Stats()
+        _check(lib().srt_render_group(self.h, C.byref(cam), C.byref(P), _ptr(acc) if want_sum else None,
+                                      _ptr(rgba) if want_rgba else None, C.byref(st)))
+        return acc, rgba, st
+
+
 class Film:
     """srt_film: progressive accumulation (the per-frame loop of glDevice::rtFrame, main.cpp:195-199, headless)."""
 

@@ -150,7 +150,7 @@ extern "C" {
 
 const char* srt_host_last_error(void) { return g_err.c_str(); }
 
-srt_status srt_prim_boxes(const srt_scene_desc* d, float time0, float time1, float* out) {
+srt_status srt_prim_boxes(const srt_scene_desc* d, float time0, float time1, float* out) try {
   if (!d || !out) return fail(SRT_ERR_INVALID, "NULL argument");
   const int64_t n = d->n_tri + d->n_sph;
   for (int64_t p = 0; p < n; p++) {
@@ -158,17 +158,17 @@ srt_status srt_prim_boxes(const srt_scene_desc* d, float time0, float time1, flo
     for (int k = 0; k < 3; k++) { out[6 * p + k] = b.mn[k]; out[6 * p + 3 + k] = b.mx[k]; }
   }
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 void srt_bvh_free(srt_bvh_node* nodes) { free(nodes); }
 
 srt_status srt_bvh_build(const srt_scene_desc* d, float time0, float time1, uint64_t rng_skip, int threads,
-                         srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) {
+                         srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) try {
   return srt_bvh_build_ordered(d, nullptr, time0, time1, rng_skip, threads, out_nodes, out_n, out_draws);
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 srt_status srt_bvh_build_ordered(const srt_scene_desc* d, const int32_t* order, float time0, float time1, uint64_t rng_skip,
-                                 int threads, srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) {
+                                 int threads, srt_bvh_node** out_nodes, int64_t* out_n, uint64_t* out_draws) try {
   if (!d || !out_nodes || !out_n) return fail(SRT_ERR_INVALID, "NULL argument");
   *out_nodes = nullptr; *out_n = 0;
   if (d->n_tri < 0 || d->n_sph < 0) return fail(SRT_ERR_INVALID, "negative count");
@@ -225,10 +225,10 @@ srt_status srt_bvh_build_ordered(const srt_scene_desc* d, const int32_t* order, 
   *out_nodes = B.nodes; *out_n = n_nodes;
   if (out_draws) *out_draws = (uint64_t)n_nodes;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 srt_status srt_camera_make(const float eye[3], const float look_at[3], const float up[3], float vfov, float aspect,
-                           float aperture, float focus_dist, float time0, float time1, srt_camera* c) {
+                           float aperture, float focus_dist, float time0, float time1, srt_camera* c) try {
   if (!eye || !look_at || !up || !c) return fail(SRT_ERR_INVALID, "NULL argument");
   const float pi = 3.1415926535897932385f;                      // globals.h:15
   const float theta = vfov * pi / 180.0f;                       // deg2rad, globals.h:26-28
@@ -250,6 +250,6 @@ srt_status srt_camera_make(const float eye[3], const float look_at[3], const flo
   c->lens_radius = aperture / 2.0f;
   c->t0 = time0; c->t1 = time1;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 }  // extern "C"

@@ -94,7 +94,7 @@ extern "C" {
 
 void srt_host_free(void* p) { free(p); }
 
-srt_status srt_png_read_memory(const uint8_t* buf, int64_t len, int32_t req_comp, int32_t* out_w, int32_t* out_h, uint8_t** out) {
+srt_status srt_png_read_memory(const uint8_t* buf, int64_t len, int32_t req_comp, int32_t* out_w, int32_t* out_h, uint8_t** out) try {
   static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
   if (!buf || !out_w || !out_h || !out) return fail(SRT_ERR_INVALID, "NULL argument");
   if (req_comp < 1 || req_comp > 4) return fail(SRT_ERR_INVALID, "req_comp must be 1..4");
@@ -141,6 +141,9 @@ srt_status srt_png_read_memory(const uint8_t* buf, int64_t len, int32_t req_comp
     const uint32_t pw = (P.w - pass[k][0] + pass[k][2] - 1) / pass[k][2], ph = (P.h - pass[k][1] + pass[k][3] - 1) / pass[k][3];
     if (pw && ph) raw_len += (((size_t)pw * ch * P.depth + 7) / 8 + 1) * ph;
   }
+  // deflate expands at most ~1032:1: a header that promises more than its IDAT bytes can hold is rejected before anything of
+  // that size is allocated (width and height are only bounded by 2^24 each)
+  if (raw_len > P.idat.size() * (size_t)1040 + 65536) return fail(SRT_ERR_INVALID, "PNG: image data too short for its dimensions");
   std::vector<uint8_t> raw(raw_len);
   uLongf got = (uLongf)raw_len;
   const int zr = uncompress(raw.data(), &got, P.idat.data(), (uLong)P.idat.size());
@@ -191,9 +194,9 @@ srt_status srt_png_read_memory(const uint8_t* buf, int64_t len, int32_t req_comp
   }
   *out = o; *out_w = (int32_t)P.w; *out_h = (int32_t)P.h;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_png_read(const char* path, int32_t req_comp, int32_t* out_w, int32_t* out_h, uint8_t** out) {
+srt_status srt_png_read(const char* path, int32_t req_comp, int32_t* out_w, int32_t* out_h, uint8_t** out) try {
   if (!path) return fail(SRT_ERR_INVALID, "NULL path");
   FILE* f = fopen(path, "rb");
   if (!f) return fail(SRT_ERR_INVALID, std::string("cannot open ") + path);
@@ -203,9 +206,9 @@ srt_status srt_png_read(const char* path, int32_t req_comp, int32_t* out_w, int3
   while ((n = fread(tmp, 1, sizeof tmp, f)) > 0) buf.insert(buf.end(), tmp, tmp + n);
   fclose(f);
   return srt_png_read_memory(buf.data(), (int64_t)buf.size(), req_comp, out_w, out_h, out);
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, const uint8_t* pixels, int32_t stride_bytes) {
+srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, const uint8_t* pixels, int32_t stride_bytes) try {
   if (!path || !pixels) return fail(SRT_ERR_INVALID, "NULL argument");
   if (w <= 0 || h <= 0 || comp < 1 || comp > 4) return fail(SRT_ERR_INVALID, "bad image size / channel count");
   if (stride_bytes == 0) stride_bytes = w * comp;
@@ -235,30 +238,39 @@ srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, c
   bool ok = fwrite(sig, 1, 8, f) == 8 && chunk("IHDR", ihdr, 13) && chunk("IDAT", z.data(), (uint32_t)clen) && chunk("IEND", nullptr, 0);
   ok = (fclose(f) == 0) && ok;
   return ok ? SRT_OK : fail(SRT_ERR_INVALID, std::string("write error on ") + path);
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 
-srt_status srt_checkpoint_write(const char* path, int32_t w, int32_t h, int32_t samples_done, uint64_t seed, const float* sum) {
+// Checkpoint file "SRTF": version 1 = {w, h, samples_done, seed, sums}; version 2 adds {sampler, max_bounce} after the seed so
+// that a resumed render can be refused when it would mix two sample streams (b200Device::rtFrameProgressive).
+srt_status srt_checkpoint_write2(const char* path, int32_t w, int32_t h, int32_t samples_done, uint64_t seed, int32_t sampler,
+                                 int32_t max_bounce, const float* sum) try {
   if (!path || !sum || w <= 0 || h <= 0 || samples_done < 0) return fail(SRT_ERR_INVALID, "bad argument");
   FILE* f = fopen(path, "wb");
   if (!f) return fail(SRT_ERR_INVALID, std::string("cannot create ") + path);
-  const uint32_t ver = 1;
+  const uint32_t ver = 2;
   const size_t n = (size_t)w * h * 3;
   bool ok = fwrite("SRTF", 1, 4, f) == 4 && fwrite(&ver, 4, 1, f) == 1 && fwrite(&w, 4, 1, f) == 1 && fwrite(&h, 4, 1, f) == 1 &&
-            fwrite(&samples_done, 4, 1, f) == 1 && fwrite(&seed, 8, 1, f) == 1 && fwrite(sum, sizeof(float), n, f) == n;
+            fwrite(&samples_done, 4, 1, f) == 1 && fwrite(&seed, 8, 1, f) == 1 && fwrite(&sampler, 4, 1, f) == 1 &&
+            fwrite(&max_bounce, 4, 1, f) == 1 && fwrite(sum, sizeof(float), n, f) == n;
   ok = (fclose(f) == 0) && ok;
   return ok ? SRT_OK : fail(SRT_ERR_INVALID, std::string("write error on ") + path);
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_checkpoint_read(const char* path, int32_t* w, int32_t* h, int32_t* samples_done, uint64_t* seed, float** out) {
+srt_status srt_checkpoint_read2(const char* path, int32_t* w, int32_t* h, int32_t* samples_done, uint64_t* seed, int32_t* sampler,
+                                int32_t* max_bounce, float** out) try {
   if (!path || !w || !h || !samples_done || !seed || !out) return fail(SRT_ERR_INVALID, "NULL argument");
   *out = nullptr;
   FILE* f = fopen(path, "rb");
   if (!f) return fail(SRT_ERR_INVALID, std::string("cannot open ") + path);
   char magic[4]; uint32_t ver = 0;
-  bool ok = fread(magic, 1, 4, f) == 4 && !memcmp(magic, "SRTF", 4) && fread(&ver, 4, 1, f) == 1 && ver == 1 && fread(w, 4, 1, f) == 1 &&
-            fread(h, 4, 1, f) == 1 && fread(samples_done, 4, 1, f) == 1 && fread(seed, 8, 1, f) == 1;
+  int32_t smp = -1, mb = -1;                       // version 1 files do not say
+  bool ok = fread(magic, 1, 4, f) == 4 && !memcmp(magic, "SRTF", 4) && fread(&ver, 4, 1, f) == 1 && (ver == 1 || ver == 2) &&
+            fread(w, 4, 1, f) == 1 && fread(h, 4, 1, f) == 1 && fread(samples_done, 4, 1, f) == 1 && fread(seed, 8, 1, f) == 1;
+  if (ok && ver == 2) ok = fread(&smp, 4, 1, f) == 1 && fread(&mb, 4, 1, f) == 1;
   if (!ok || *w <= 0 || *h <= 0 || *samples_done < 0 || (int64_t)*w * *h > (1ll << 32)) { fclose(f); return fail(SRT_ERR_INVALID, "not a checkpoint file"); }
+  if (sampler) *sampler = smp;
+  if (max_bounce) *max_bounce = mb;
   const size_t n = (size_t)*w * *h * 3;
   float* p = (float*)malloc(n * sizeof(float));
   if (!p) { fclose(f); return fail(SRT_ERR_NOMEM, "checkpoint buffer"); }
@@ -267,6 +279,13 @@ srt_status srt_checkpoint_read(const char* path, int32_t* w, int32_t* h, int32_t
   if (!full) { free(p); return fail(SRT_ERR_INVALID, "truncated checkpoint file"); }
   *out = p;
   return SRT_OK;
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
+
+srt_status srt_checkpoint_write(const char* path, int32_t w, int32_t h, int32_t samples_done, uint64_t seed, const float* sum) {
+  return srt_checkpoint_write2(path, w, h, samples_done, seed, -1, -1, sum);
+}
+srt_status srt_checkpoint_read(const char* path, int32_t* w, int32_t* h, int32_t* samples_done, uint64_t* seed, float** out) {
+  return srt_checkpoint_read2(path, w, h, samples_done, seed, nullptr, nullptr, out);
 }
 
 }  // extern "C"

@@ -134,7 +134,7 @@ hittableList randomScene(const std::string& dataDir, std::vector<shared_ptr<mode
 
 extern "C" {
 
-srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_scene** out) {
+srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_scene** out) try {
   if (!out || !data_dir) return fail(SRT_ERR_INVALID, "NULL argument");
   *out = nullptr;
   std::string dir(data_dir);
@@ -144,9 +144,9 @@ srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_sc
   if (!referenceScene(which, dir, *S, err)) { delete S; return fail(SRT_ERR_INVALID, err); }
   *out = S;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
-srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int options, srt_host_scene** out) {
+srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int options, srt_host_scene** out) try {
   if (!out || !gltf_path) return fail(SRT_ERR_INVALID, "NULL argument");
   *out = nullptr;
   auto* S = new srt_host_scene;
@@ -166,7 +166,7 @@ srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, i
   if (!S->flat.build(S->world)) { const std::string e = S->flat.error; delete S; return fail(SRT_ERR_INVALID, e); }
   *out = S;
   return SRT_OK;
-}
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
 
 const srt_scene_desc* srt_host_scene_desc(const srt_host_scene* s) { return s ? &s->flat.desc() : nullptr; }
 uint64_t srt_host_scene_draws(const srt_host_scene* s) { return s ? s->draws : 0; }

@@ -407,15 +407,28 @@ struct Gltf {
     const auto& bv = views->at(vi);
     const long bi = bv.index("buffer");
     if (bi < 0 || (size_t)bi >= buffers.size()) return false;
-    size_t off = (size_t)bv.number("byteOffset", 0);
+    // every number below comes from an untrusted file: reject anything that is not a finite integer in [0, 2^53] before it
+    // is cast, and check the range without arithmetic that could wrap
+    auto field = [](const srt_json::Value& v, const char* key, size_t& out) -> bool {
+      const double d = v.number(key, 0);
+      if (!(d >= 0.0) || !(d <= 9007199254740992.0) || d != std::floor(d)) return false;
+      out = (size_t)d;
+      return true;
+    };
+    const size_t size = buffers[bi].size();
+    size_t off = 0, acc_off = 0, bs = 0, view_len = 0;
+    if (!field(bv, "byteOffset", off) || !field(*acc, "byteOffset", acc_off) || !field(bv, "byteStride", bs) ||
+        !field(*acc, "count", count) || !field(bv, "byteLength", view_len)) return false;
+    if (off > size) return false;
+    size_t avail = size - off;                                   // bytes from the view's start to the end of the buffer
+    if (bv.get("byteLength")) { if (view_len > avail) return false; if (!g_gltf.referenceQuirks) avail = view_len; }
     stride = elem_bytes;
     if (!g_gltf.referenceQuirks) {
-      off += (size_t)acc->number("byteOffset", 0);
-      const size_t bs = (size_t)bv.number("byteStride", 0);
-      if (bs) stride = bs;
+      if (acc_off > avail) return false;
+      off += acc_off; avail -= acc_off;
+      if (bs) { if (bs < elem_bytes) return false; stride = bs; }
     }
-    count = (size_t)acc->number("count", 0);
-    if (count && off + (count - 1) * stride + elem_bytes > buffers[bi].size()) return false;
+    if (count && (elem_bytes > avail || (count - 1) > (avail - elem_bytes) / stride)) return false;
     ptr = buffers[bi].data() + off;
     return true;
   }
@@ -617,11 +630,14 @@ bool gltfLoad(std::string filename, shared_ptr<model> mdl) {
 // ---- b200Device ---------------------------------------------------------------------------------------------------------
 namespace {
 struct Api {
-  srt_status (*device_create)(int, srt_device**);
-  void (*device_destroy)(srt_device*);
-  srt_status (*scene_create)(srt_device*, const srt_scene_desc*, srt_scene**);
-  void (*scene_destroy)(srt_scene*);
-  srt_status (*render)(srt_scene*, const srt_camera*, const srt_render_params*, float*, uint8_t*, srt_stats*);
+  srt_status (*group_create)(const int*, int, srt_device_group**);
+  void (*group_destroy)(srt_device_group*);
+  int32_t (*group_size)(const srt_device_group*);
+  srt_device* (*group_device)(srt_device_group*, int32_t);
+  srt_status (*scene_group_create)(srt_device_group*, const srt_scene_desc*, srt_scene_group**);
+  void (*scene_group_destroy)(srt_scene_group*);
+  srt_scene* (*scene_group_scene)(srt_scene_group*, int32_t);
+  srt_status (*render_group)(srt_scene_group*, const srt_camera*, const srt_render_params*, float*, uint8_t*, srt_stats*);
   const char* (*last_error)(void);
   srt_status (*film_create)(srt_device*, int32_t, int32_t, srt_film**);
   void (*film_destroy)(srt_film*);
@@ -631,11 +647,14 @@ struct Api {
   srt_status (*film_load)(srt_film*, const float*, int32_t);
 };
 bool bind(void* so, Api& a) {
-  a.device_create = (decltype(a.device_create))dlsym(so, "srt_device_create");
-  a.device_destroy = (decltype(a.device_destroy))dlsym(so, "srt_device_destroy");
-  a.scene_create = (decltype(a.scene_create))dlsym(so, "srt_scene_create");
-  a.scene_destroy = (decltype(a.scene_destroy))dlsym(so, "srt_scene_destroy");
-  a.render = (decltype(a.render))dlsym(so, "srt_render");
+  a.group_create = (decltype(a.group_create))dlsym(so, "srt_device_group_create");
+  a.group_destroy = (decltype(a.group_destroy))dlsym(so, "srt_device_group_destroy");
+  a.group_size = (decltype(a.group_size))dlsym(so, "srt_device_group_size");
+  a.group_device = (decltype(a.group_device))dlsym(so, "srt_device_group_device");
+  a.scene_group_create = (decltype(a.scene_group_create))dlsym(so, "srt_scene_group_create");
+  a.scene_group_destroy = (decltype(a.scene_group_destroy))dlsym(so, "srt_scene_group_destroy");
+  a.scene_group_scene = (decltype(a.scene_group_scene))dlsym(so, "srt_scene_group_scene");
+  a.render_group = (decltype(a.render_group))dlsym(so, "srt_render_group");
   a.last_error = (decltype(a.last_error))dlsym(so, "srt_last_error");
   a.film_create = (decltype(a.film_create))dlsym(so, "srt_film_create");
   a.film_destroy = (decltype(a.film_destroy))dlsym(so, "srt_film_destroy");
@@ -643,12 +662,17 @@ bool bind(void* so, Api& a) {
   a.film_samples = (decltype(a.film_samples))dlsym(so, "srt_film_samples");
   a.film_resolve = (decltype(a.film_resolve))dlsym(so, "srt_film_resolve");
   a.film_load = (decltype(a.film_load))dlsym(so, "srt_film_load");
-  return a.device_create && a.device_destroy && a.scene_create && a.scene_destroy && a.render && a.last_error && a.film_create &&
+  return a.group_create && a.group_destroy && a.group_size && a.group_device && a.scene_group_create && a.scene_group_destroy &&
+         a.scene_group_scene && a.render_group && a.last_error && a.film_create &&
          a.film_destroy && a.film_add && a.film_samples && a.film_resolve && a.film_load;
 }
 }  // namespace
 
-bool b200Device::init(int, int, const hittableList& world, int gpu, const char* library_path) {
+bool b200Device::init(int w, int h, const hittableList& world, int gpu, const char* library_path) {
+  return init(w, h, world, gpu < 0 ? std::vector<int>() : std::vector<int>(1, gpu), library_path);
+}
+
+bool b200Device::init(int, int, const hittableList& world, const std::vector<int>& gpus, const char* library_path) {
   terminate();
   flatScene flat;
   if (!flat.build(world)) { err = flat.error; return false; }
@@ -657,8 +681,11 @@ bool b200Device::init(int, int, const hittableList& world, int gpu, const char* 
   if (!so) { err = std::string("cannot load the CUDA library (there is no CPU fallback): ") + dlerror(); return false; }
   Api a;
   if (!bind(so, a)) { err = "libsrt_b200.so lacks an entry point of include/srt.h"; return false; }
-  if (a.device_create(gpu, &dev) != SRT_OK) { err = a.last_error(); dev = nullptr; return false; }
-  if (a.scene_create(dev, &flat.desc(), &scene) != SRT_OK) { err = a.last_error(); scene = nullptr; return false; }
+  // one device per GPU of the list (empty = every visible GPU), one replica of the scene on each (glDevice::init's upload)
+  if (a.group_create(gpus.empty() ? nullptr : gpus.data(), (int)gpus.size(), &group) != SRT_OK) { err = a.last_error(); group = nullptr; return false; }
+  if (a.scene_group_create(group, &flat.desc(), &scenes) != SRT_OK) { err = a.last_error(); scenes = nullptr; return false; }
+  dev = a.group_device(group, 0);                 // progressive films live on the first GPU
+  scene = a.scene_group_scene(scenes, 0);
   return true;
 }
 
@@ -672,7 +699,7 @@ bool b200Device::rtFrame(void* frameData, int w, int h, const camera& cam, const
   p.width = w; p.height = h; p.spp = numSamples; p.max_bounce = maxBounce; p.seed = seed; p.sampler = sampler;
   for (int k = 0; k < 3; k++) p.background[k] = background(k);
   srt_stats st;
-  if (a.render(scene, &cam.desc(), &p, nullptr, static_cast<uint8_t*>(frameData), &st) != SRT_OK) { err = a.last_error(); return false; }
+  if (a.render_group(scenes, &cam.desc(), &p, nullptr, static_cast<uint8_t*>(frameData), &st) != SRT_OK) { err = a.last_error(); return false; }
   if (stats) *stats = st;
   return true;
 }
@@ -687,7 +714,12 @@ bool b200Device::rtFrameProgressive(void* frameData, int w, int h, const camera&
     if (a.film_create(dev, w, h, &film) != SRT_OK) { err = a.last_error(); film = nullptr; return false; }
     film_w = w; film_h = h;
   }
-  film_seed = seed;
+  if (a.film_samples(film) > 0 &&
+      (seed != film_seed || (film_sampler >= 0 && sampler != film_sampler) || (film_bounce >= 0 && maxBounce != film_bounce))) {
+    err = "rtFrameProgressive: the film already holds samples of another seed / sampler / maxBounce (resetFilm() starts a new one)";
+    return false;
+  }
+  film_seed = seed; film_sampler = sampler; film_bounce = maxBounce;
   srt_render_params p;
   memset(&p, 0, sizeof p);
   p.width = w; p.height = h; p.max_bounce = maxBounce; p.seed = seed; p.sampler = sampler;
@@ -699,11 +731,24 @@ bool b200Device::rtFrameProgressive(void* frameData, int w, int h, const camera&
   return true;
 }
 
+int b200Device::gpuCount() const {
+  if (!group) return 0;
+  Api a;
+  return bind(so, a) ? a.group_size(group) : 0;
+}
+
 int b200Device::samplesDone() const {
   if (!film) return 0;
   Api a;
   bind(so, a);
   return a.film_samples(film);
+}
+
+void b200Device::resetFilm() {
+  if (!film) return;
+  Api a;
+  if (bind(so, a)) a.film_destroy(film);
+  film = nullptr; film_sampler = film_bounce = -1;
 }
 
 bool b200Device::saveCheckpoint(const char* path) {
@@ -712,7 +757,7 @@ bool b200Device::saveCheckpoint(const char* path) {
   bind(so, a);
   std::vector<float> sum((size_t)film_w * film_h * 3);
   if (a.film_resolve(film, nullptr, sum.data()) != SRT_OK) { err = a.last_error(); return false; }
-  if (srt_checkpoint_write(path, film_w, film_h, a.film_samples(film), film_seed, sum.data()) != SRT_OK) { err = srt_host_last_error(); return false; }
+  if (srt_checkpoint_write2(path, film_w, film_h, a.film_samples(film), film_seed, film_sampler, film_bounce, sum.data()) != SRT_OK) { err = srt_host_last_error(); return false; }
   return true;
 }
 
@@ -720,14 +765,14 @@ bool b200Device::loadCheckpoint(const char* path, int w, int h) {
   if (!scene) { err = "loadCheckpoint before init"; return false; }
   Api a;
   bind(so, a);
-  int32_t cw = 0, ch = 0, done = 0;
+  int32_t cw = 0, ch = 0, done = 0, smp = -1, mb = -1;
   uint64_t seed = 0;
   float* sum = nullptr;
-  if (srt_checkpoint_read(path, &cw, &ch, &done, &seed, &sum) != SRT_OK) { err = srt_host_last_error(); return false; }
+  if (srt_checkpoint_read2(path, &cw, &ch, &done, &seed, &smp, &mb, &sum) != SRT_OK) { err = srt_host_last_error(); return false; }
   if (cw != w || ch != h) { srt_host_free(sum); err = "checkpoint is of a different frame size"; return false; }
   if (film && (film_w != w || film_h != h)) { a.film_destroy(film); film = nullptr; }
   if (!film && a.film_create(dev, w, h, &film) != SRT_OK) { srt_host_free(sum); err = a.last_error(); film = nullptr; return false; }
-  film_w = w; film_h = h; film_seed = seed;
+  film_w = w; film_h = h; film_seed = seed; film_sampler = smp; film_bounce = mb;
   const srt_status rc = a.film_load(film, sum, done);
   srt_host_free(sum);
   if (rc != SRT_OK) { err = a.last_error(); return false; }
@@ -739,12 +784,12 @@ void b200Device::terminate() {
     Api a;
     if (bind(so, a)) {
       if (film) a.film_destroy(film);
-      if (scene) a.scene_destroy(scene);
-      if (dev) a.device_destroy(dev);
+      if (scenes) a.scene_group_destroy(scenes);
+      if (group) a.group_destroy(group);
     }
     dlclose(so);
   }
-  so = nullptr; dev = nullptr; scene = nullptr; film = nullptr;
+  so = nullptr; dev = nullptr; scene = nullptr; film = nullptr; group = nullptr; scenes = nullptr;
 }
 
 }  // namespace srt

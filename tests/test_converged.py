@@ -50,8 +50,13 @@ def tile_spread(t, ref, spp):
 
 def check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp_gpu, median_cap, factor, psnr_margin):
     spp_ref = int(g["spp"])
+    # a NaN sample poisons its pixel for good (the reference's does too: globals.h:61-70 normalises zero vectors); the
+    # rate per SAMPLE has to stay the reference's own, counted in its two golden frames (3e-8 .. 1.4e-7)
+    bad_ref = float(1.0 - ok.mean()) / (2 * spp_ref)
+    bad_gpu = float(1.0 - np.isfinite(got).all(axis=2).mean()) / spp_gpu
+    assert bad_gpu <= 4.0 * bad_ref + 2e-8, "non-finite pixels per sample: GPU %.3g, reference %.3g" % (bad_gpu, bad_ref)
     ok = ok & np.isfinite(got).all(axis=2)
-    assert ok.mean() > 0.9999
+    assert ok.mean() > 0.999
     floor = float(g["psnr_ab"])
     pa, pb = psnr_u8(rgba, ra, ok), psnr_u8(rgba, rb, ok)
     assert min(pa, pb) >= floor + psnr_margin, "PSNR vs A %.2f dB, vs B %.2f dB; reference A/B floor %.2f dB" % (pa, pb, floor)

@@ -397,3 +397,84 @@ def test_example_progressive_resumes(tmp_path):
     assert done == 16
     a, b = host.png_read(one, 4), host.png_read(prog, 4)
     assert a.shape == b.shape and (np.abs(a.astype(int) - b.astype(int)) <= 1).mean() > 0.999
+
+
+@pytest.mark.gpu
+def test_example_refuses_to_mix_sample_streams(tmp_path):
+    """a checkpoint records seed, sampler and depth (SRTF version 2): resuming it with another seed would continue the global
+    sample indices with different draws - b200Device::rtFrameProgressive refuses."""
+    from sexy_raytracer_b200 import build
+    exe = build.build_example()
+    env = dict(os.environ, SRT_B200_LIBRARY=build.LIB)
+    prog = str(tmp_path / "mix.png")
+    assert subprocess.run([exe, "shirley", "90", "8", prog, "2", "1"], capture_output=True, env=env).returncode == 0
+    r = subprocess.run([exe, "shirley", "90", "16", prog, "4", "2"], capture_output=True, text=True, env=env)       # other seed
+    assert r.returncode != 0 and "another seed" in r.stderr
+    _, done, seed = host.checkpoint_read(prog + ".srtf")
+    assert done == 8 and seed == 1                                 # the checkpoint is untouched
+
+
+def test_checkpoint_version2_round_trip(tmp_path):
+    import ctypes as C
+    L = host._bind_world(host.lib())
+    L.srt_checkpoint_write2.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.c_uint64, C.c_int32, C.c_int32, C.c_void_p]
+    L.srt_checkpoint_read2.argtypes = [C.c_char_p] + [C.POINTER(C.c_int32)] * 3 + [C.POINTER(C.c_uint64)] + [C.POINTER(C.c_int32)] * 2 + \
+        [C.POINTER(C.POINTER(C.c_float))]
+    a = np.random.default_rng(1).random((5, 7, 3)).astype(np.float32)
+    p = str(tmp_path / "v2.srtf").encode()
+    assert L.srt_checkpoint_write2(p, 7, 5, 40, 99, 1, 6, a.ctypes.data_as(C.c_void_p)) == 0
+    w, h, n, smp, mb = (C.c_int32() for _ in range(5))
+    seed = C.c_uint64()
+    out = C.POINTER(C.c_float)()
+    assert L.srt_checkpoint_read2(p, C.byref(w), C.byref(h), C.byref(n), C.byref(seed), C.byref(smp), C.byref(mb), C.byref(out)) == 0
+    assert (w.value, h.value, n.value, seed.value, smp.value, mb.value) == (7, 5, 40, 99, 1, 6)
+    assert (np.ctypeslib.as_array(out, shape=(105,)) == a.ravel()).all()
+    L.srt_host_free(out)
+    b, n1, seed1 = host.checkpoint_read(p.decode())               # the version-1 entry point reads version-2 files too
+    assert n1 == 40 and seed1 == 99 and (b == a).all()
+    host.checkpoint_write(p.decode(), a, 3, seed=5)                # ... and what it writes carries "not recorded"
+    assert L.srt_checkpoint_read2(p, C.byref(w), C.byref(h), C.byref(n), C.byref(seed), C.byref(smp), C.byref(mb), C.byref(out)) == 0
+    assert (smp.value, mb.value) == (-1, -1)
+    L.srt_host_free(out)
+
+
+def test_gltf_rejects_malformed_accessors(tmp_path):
+    """accessor / bufferView numbers come from an untrusted file: negative, fractional, huge and wrapping values, strides below
+    the element size and views past the buffer are rejected, not read."""
+    import base64
+    import json
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32).tobytes()
+    idx = np.array([0, 1, 2], np.uint16).tobytes()
+    blob = pos + idx + b"\0\0"
+
+    def doc(**over):
+        d = {"asset": {"version": "2.0"}, "buffers": [{"byteLength": len(blob), "uri": "data:application/octet-stream;base64," + base64.b64encode(blob).decode()}],
+             "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": 36}, {"buffer": 0, "byteOffset": 36, "byteLength": 6}],
+             "accessors": [{"bufferView": 0, "componentType": 5126, "count": 3, "type": "VEC3"},
+                           {"bufferView": 1, "componentType": 5123, "count": 3, "type": "SCALAR"}],
+             "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [1, 1, 1, 1]}}],
+             "meshes": [{"primitives": [{"attributes": {"POSITION": 0}, "indices": 1, "material": 0}]}], "nodes": [{"mesh": 0}], "scenes": [{"nodes": [0]}]}
+        for path, v in over.items():
+            a, i, k = path.split("/")
+            d[a][int(i)][k] = v
+        return d
+
+    def load(d, quirks):
+        p = str(tmp_path / "m.gltf")
+        open(p, "w").write(json.dumps(d))
+        try:
+            return host.gltf_scene(p, str(tmp_path) + "/", reference_quirks=quirks)
+        except Exception:
+            return None
+    good = load(doc(), False)
+    assert good is not None and good.n_tri == 1
+    bad = [{"accessors/0/count": 2 ** 61}, {"accessors/0/count": -3}, {"accessors/0/count": 1e300}, {"accessors/0/count": 2.5},
+           {"bufferViews/0/byteOffset": -8}, {"bufferViews/0/byteOffset": 2 ** 64}, {"bufferViews/0/byteOffset": 40},
+           {"accessors/0/byteOffset": 2 ** 63}, {"accessors/0/byteOffset": 30}, {"bufferViews/0/byteStride": 4},
+           {"bufferViews/0/byteStride": 2 ** 62}, {"bufferViews/0/byteLength": 10 ** 9}, {"accessors/1/count": 2 ** 40},
+           {"bufferViews/1/byteOffset": 2 ** 53 + 2}]
+    for over in bad:
+        for quirks in (False, True):
+            s = load(doc(**over), quirks)
+            assert s is None or s.n_tri <= 1, over      # either refused, or (a field the reference's rules ignore) loaded in bounds
+        assert load(doc(**over), False) is None, over
