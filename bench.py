@@ -447,6 +447,66 @@ def run_b200(args):
         emit(line)
 
 
+# ---- the same frame through the C entry point that owns the whole box: srt_render_group (one process, one host thread per GPU,
+# peer copies instead of NCCL).  `python bench.py --backend group --gpus N` - NOT under torch.distributed.run.
+def run_group(args):
+    import zlib
+    if int(os.environ.get("RANK", "0")) != 0:
+        return                                   # launched under torchrun by mistake: rank 0 alone drives the box
+    from sexy_raytracer_b200.device import DeviceGroup
+    scene, W, H, spp, depth = load_workload(args)
+    grp = DeviceGroup(list(range(args.gpus)))
+    n = len(grp)
+    sg = grp.upload(scene)
+    P = scene.render_params(width=W, height=H, spp=spp, max_bounce=depth, seed=2026, variant=args.variant)
+    for _ in range(args.warmup):
+        sg.render(P, want_sum=False, want_rgba=True)
+    clocks = ClockSampler(0)
+    clocks.start()
+    seg = paths = launches = 0
+    kern_ms = 0.0
+    st = None
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        acc, frame, st = sg.render(P, want_sum=False, want_rgba=True)
+        seg += int(st.segments); paths += int(st.paths); launches += int(st.launches); kern_ms += st.kernel_ms
+    wall = time.perf_counter() - t0
+    clk = clocks.stop()
+    acc, frame, st = sg.render(P, want_sum=True, want_rgba=True)
+    crc = "%08x" % (zlib.crc32(frame.tobytes()) & 0xffffffff)
+    sum_total = float(np.nan_to_num(acc.astype(np.float64), nan=0.0, posinf=0.0, neginf=0.0).sum())
+    if args.save_frame:
+        np.save(args.save_frame, frame)
+    # e2e: replicas created, frame rendered, replicas destroyed - every step
+    e2e_seg, e2e_steps = 0, []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        t1 = time.perf_counter()
+        sg2 = grp.upload(scene)
+        _, _, st2 = sg2.render(P, want_sum=False, want_rgba=True)
+        sg2.close()
+        e2e_seg += int(st2.segments)
+        e2e_steps.append(round(time.perf_counter() - t1, 4))
+    e2e_s = time.perf_counter() - t0
+    sg.close()
+    grp.close()
+    emit({"metric": METRIC, "value": round(seg / wall / 1e6, 2), "unit": "M segments/s", "n_gpus": n, "steps": args.steps,
+          "warmup": args.warmup, "ms_per_step": round(wall / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "strong",
+          "vs_baseline": None, "dtype": "f32", "data": "synthetic", "backend": "group",
+          "timing": "host clock around srt_render_group (scene replicas resident; the call ends with the RGBA8 frame on the host and "
+                    "every GPU synchronised); render_kernel_ms_per_step = CUDA events inside the library, slowest GPU",
+          "config": {"workload": WORKLOAD_NAMES[args.config] + (" [spp overridden: %d]" % spp if args.spp else ""),
+                     "width": W, "height": H, "spp": spp, "max_bounce": depth, "parallelism": "spp-split x%d, srt_render_group" % n,
+                     "l2": "no flush: 8 Mi path slots (0.5 GB) stream through the L2 every wave"},
+          "frame_time_s": round(wall / args.steps, 4), "segments_per_step": seg / args.steps, "paths_per_step": paths / args.steps,
+          "render_kernel_ms_per_step": round(kern_ms / args.steps, 3),
+          "e2e": {"value": round(e2e_seg / e2e_s / 1e6, 2), "unit": "M segments/s", "h2d_bytes_per_step": scene.host_bytes() * n,
+                  "d2h_bytes_per_step": W * H * 4, "s_per_step": round(e2e_s / args.steps, 4), "s_steps": e2e_steps,
+                  "path": "srt_scene_group_create(host SoA) + srt_render_group(host RGBA8 out) + srt_scene_group_destroy"},
+          "gpu_launches": launches, "variant": int(st.variant), "frame_crc": crc, "sum_total": sum_total, "clocks": clk,
+          "roofline": None, "cpu_baseline": None})
+
+
 # ---- the reference arm: the reference's own CPU code, all host cores ----------------------------------------------
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -503,6 +563,8 @@ def main():
     ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
     ap.add_argument("--spp", type=int, default=0, help="override the samples per pixel of the config (not the headline)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--backend", default="ranks", choices=["ranks", "group"],
+                    help="ranks: one process per GPU (torch.distributed.run, NCCL reduce); group: ONE process, srt_render_group over --gpus GPUs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--tris", type=int, default=10_000_000, help="config c5: triangles")
     ap.add_argument("--spheres", type=int, default=100_000, help="config c5: spheres")
@@ -511,6 +573,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.backend == "group":
+        run_group(args)
     else:
         run_b200(args)
 

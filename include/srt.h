@@ -203,7 +203,7 @@ typedef struct srt_stats {
   int32_t  extend_launches;
   int32_t  variant;        /* the variant that ran: 1 flat megakernel, 2 wavefront, 3 phased megakernel */
   int32_t  extend_kernel;  /* variant 2: 0 = k_wf_extend (exact ordered walk), 16 / 32 = k_wf_extend2 with 16- / 32-byte nodes */
-  int32_t  reserved0;
+  int32_t  fused;          /* variant 2: 1 = the frame ran as ONE launch of k_wf_path (extend + shade in one persistent kernel) */
 } srt_stats;
 
 typedef struct srt_device srt_device;

@@ -74,7 +74,7 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("segments", C.c_uint64), ("node_visits", C.c_uint64),
                 ("leaf_tests", C.c_uint64), ("kernel_ms", C.c_float), ("launches", C.c_int32),
                 ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("extend_launches", C.c_int32), ("variant", C.c_int32),
-                ("extend_kernel", C.c_int32), ("reserved0", C.c_int32)]
+                ("extend_kernel", C.c_int32), ("fused", C.c_int32)]
 
 
 # numpy dtypes with the same layout (for bulk arrays of rays / hits / nodes)

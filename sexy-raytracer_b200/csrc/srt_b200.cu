@@ -15,6 +15,7 @@
 #include "srt_phased.cuh"
 #include "srt_wavefront.cuh"
 #include "srt_extend2.cuh"
+#include "srt_path.cuh"
 
 using namespace srt;
 
@@ -51,6 +52,8 @@ struct srt_device {
   float* d_frame_sum = nullptr; uchar4* d_frame_rgba = nullptr; size_t frame_cap = 0;   // srt_render's device buffers (pixels)
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
+  void* d_path = nullptr; size_t path_capacity = 0;  // k_wf_path's warp-private path slots (srt_path.cuh)
+  void* h_stage = nullptr; size_t h_stage_cap = 0;  // pinned staging of srt_scene_create's arena (scenes up to SCENE_STAGE_MAX bytes)
 };
 static const int WF_RING = 8;
 static const int WF_TRING = 16;
@@ -116,7 +119,9 @@ void srt_device_destroy(srt_device* d) {
   if (d->d_sort_tmp) cudaFree(d->d_sort_tmp);
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
+  if (d->d_path) cudaFree(d->d_path);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
+  if (d->h_stage) cudaFreeHost(d->h_stage);
   for (int k = 0; k < WF_RING; k++) if (d->wf_ev[k]) cudaEventDestroy(d->wf_ev[k]);
   for (int k = 0; k < WF_TRING; k++) for (int q = 0; q < 3; q++) if (d->wf_t[k][q]) cudaEventDestroy(d->wf_t[k][q]);
   if (d->ev0) cudaEventDestroy(d->ev0);
@@ -206,19 +211,47 @@ static srt_status thread_bvh(const srt_scene_desc* d, std::vector<Node>& out, bo
   return SRT_OK;
 }
 
-template <typename T>
-static srt_status upload(srt_scene* s, const std::vector<T>& v, const T** dptr) {
-  void* p = nullptr;
-  size_t nb = v.size() * sizeof(T);
-  cudaError_t e = cudaMalloc(&p, nb ? nb : 16);
-  if (e != cudaSuccess) { cudaGetLastError(); return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
-  s->buffers.push_back(p);
-  if (nb) CK(cudaMemcpyAsync(p, v.data(), nb, cudaMemcpyHostToDevice, s->dev->stream));
-  CK(cudaStreamSynchronize(s->dev->stream));   // v is a temporary of the caller
-  s->bytes += (int64_t)nb;
-  *dptr = static_cast<const T*>(p);
-  return SRT_OK;
-}
+// The device side of a scene is ONE allocation: every table is laid out in it at a 256-byte boundary, gathered in a pinned
+// staging buffer of the device object and copied with one cudaMemcpyAsync; the set-up kernels follow on the same stream and
+// srt_scene_create synchronises once, at its end.  (A dozen cudaMalloc + blocking copies cost 4.5 ms per scene, and as many
+// cudaFree calls at destroy - per frame in the reference's flow, glDevice::rtFrame.)  Scenes beyond SCENE_STAGE_MAX bytes
+// copy table by table from the caller's pageable memory instead of doubling their size in pinned memory.
+static const size_t SCENE_STAGE_MAX = (size_t)64 << 20;
+struct SceneArena {
+  struct Item { const void* src; size_t nb, off; const void** dst; };
+  std::vector<Item> items;
+  size_t total = 0;
+  template <typename T>
+  void add(const std::vector<T>& v, const T** dptr) { reserve(v.data(), v.size() * sizeof(T), reinterpret_cast<const void**>(dptr)); }
+  void reserve(const void* src, size_t nb, const void** dptr) {
+    items.push_back({src, nb, total, dptr});
+    total += (std::max<size_t>(nb, 16) + 255) & ~(size_t)255;
+  }
+  // allocate + enqueue the copies on the device's stream; the sources must stay alive until the stream is synchronised
+  srt_status commit(srt_scene* s) {
+    srt_device* dev = s->dev;
+    void* base = nullptr;
+    cudaError_t e = cudaMalloc(&base, total ? total : 256);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
+    s->buffers.push_back(base);
+    const bool staged = total <= SCENE_STAGE_MAX;
+    if (staged && dev->h_stage_cap < total) {
+      if (dev->h_stage) { CK(cudaFreeHost(dev->h_stage)); dev->h_stage = nullptr; dev->h_stage_cap = 0; }
+      const size_t cap = std::max<size_t>(total, (size_t)4 << 20);
+      CK(cudaMallocHost(&dev->h_stage, cap));
+      dev->h_stage_cap = cap;
+    }
+    for (const Item& it : items) {
+      *it.dst = static_cast<const char*>(base) + it.off;
+      s->bytes += (int64_t)it.nb;
+      if (!it.src || !it.nb) continue;
+      if (staged) memcpy(static_cast<char*>(dev->h_stage) + it.off, it.src, it.nb);
+      else CK(cudaMemcpyAsync(static_cast<char*>(base) + it.off, it.src, it.nb, cudaMemcpyHostToDevice, dev->stream));
+    }
+    if (staged && total) CK(cudaMemcpyAsync(base, dev->h_stage, total, cudaMemcpyHostToDevice, dev->stream));
+    return SRT_OK;
+  }
+};
 
 static bool tex_is_image(const srt_scene_desc* d, int id) {
   if (id < 0) return false;
@@ -281,7 +314,8 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     Node t; t.lo = make_float4(0, 0, 0, 0); t.hi = make_float4(0, 0, i2f(-1), i2f(NODE_NO_BOX));
     for (int k = 0; k < 4; k++) nodes.push_back(t);      // + 3 of padding: the walk may prefetch up to 3 nodes ahead
   }
-  SCK(upload(s, nodes, &s->sc.nodes));
+  SceneArena arena;
+  arena.add(nodes, &s->sc.nodes);
   s->sc.n_nodes = n_real;
   s->sc.filter_ok = filter_ok ? 1 : 0;
   s->node_bytes = (size_t)(n_real + 1) * sizeof(Node);
@@ -322,6 +356,8 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
 
   // compact tree + leaf-ordered primitives for trees that stay in HBM (srt_core.cuh)
   std::vector<int32_t> lp_src;            // leaf order -> original primitive id
+  std::vector<uint4> cn;
+  bool have_cn = false;
   s->sc.cnodes = nullptr; s->sc.lprims = nullptr;
   if (!s->nodes_in_smem && filter_ok && n_real > 0 && d->n_tri + d->n_sph < (int64_t)CNODE_NO_PRIM - 1) {
     const Node& root = nodes[0];
@@ -334,7 +370,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       s->sc.q_org[k] = rlo[k]; s->sc.q_cell[k] = c;
       org[k] = rlo[k]; cell[k] = c;
     }
-    std::vector<uint4> cn(nodes.size());
+    cn.resize(nodes.size());
     auto snap = [&](double v, int k, bool up) -> uint32_t {
       double g = (v - org[k]) / cell[k];
       g = up ? std::ceil(g) : std::floor(g);
@@ -370,7 +406,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       }
       cn[i] = q;
     }
-    if (ok) SCK(upload(s, cn, &s->sc.cnodes));
+    if (ok && !lp_src.empty()) { arena.add(cn, &s->sc.cnodes); have_cn = true; }
     else lp_src.clear();
   }
 
@@ -383,18 +419,19 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     uvs[i].a = make_float4(d->tri_uv0[2 * i], d->tri_uv0[2 * i + 1], d->tri_uv1[2 * i], d->tri_uv1[2 * i + 1]);
     uvs[i].b = make_float4(d->tri_uv2[2 * i], d->tri_uv2[2 * i + 1], 0, 0);
   }
-  SCK(upload(s, tris, &s->sc.tris));
-  SCK(upload(s, uvs, &s->sc.tri_uv));
+  arena.add(tris, &s->sc.tris);
+  arena.add(uvs, &s->sc.tri_uv);
   s->sc.n_tri = (int)d->n_tri;
   s->sc.tri_vn = nullptr;
+  std::vector<float4> vn;
   if (d->n_tri > 0 && (d->tri_n0 || d->tri_n1 || d->tri_n2)) {
     if (!d->tri_n0 || !d->tri_n1 || !d->tri_n2) { srt_scene_destroy(s); return fail(SRT_ERR_INVALID, "tri_n0, tri_n1, tri_n2: all three or none"); }
-    std::vector<float4> vn((size_t)d->n_tri * 3);
+    vn.resize((size_t)d->n_tri * 3);
     for (int64_t i = 0; i < d->n_tri; i++) {
       const float* n[3] = {d->tri_n0 + 3 * i, d->tri_n1 + 3 * i, d->tri_n2 + 3 * i};
       for (int k = 0; k < 3; k++) vn[3 * i + k] = make_float4(n[k][0], n[k][1], n[k][2], 0);
     }
-    SCK(upload(s, vn, &s->sc.tri_vn));
+    arena.add(vn, &s->sc.tri_vn);
   }
   std::vector<Sph> sphs((size_t)d->n_sph);
   for (int64_t j = 0; j < d->n_sph; j++) {
@@ -404,7 +441,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     sphs[j].b = make_float4(b[0], b[1], b[2], d->sph_t0[j]);
     sphs[j].c = make_float4(d->sph_t1[j], i2f(d->sph_mat[j]), moving ? 1.0f : 0.0f, 0);
   }
-  SCK(upload(s, sphs, &s->sc.sphs));
+  arena.add(sphs, &s->sc.sphs);
   s->sc.n_sph = (int)d->n_sph;
 
   // textures: texel (i,j) = (px[0],px[1],px[2],255), px = data + j*bpp*w + i*bpp; bytes past the end read 0
@@ -442,7 +479,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     }
     texs[i] = x;
   }
-  SCK(upload(s, texs, &s->sc.texs));
+  arena.add(texs, &s->sc.texs);
   s->sc.n_tex = d->n_tex;
 
   std::vector<Mat> mats((size_t)d->n_mat);
@@ -460,33 +497,29 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     if (m.kind == SRT_MAT_PBR && (m.flags & SRT_MATF_PACKED_MR) && x.metallic_tex >= 0) { x.flags |= MAT_PACKED_MR; x.roughness_tex = -1; }
     mats[i] = x;
   }
-  SCK(upload(s, mats, &s->sc.mats));
+  arena.add(mats, &s->sc.mats);
   s->sc.n_mat = d->n_mat;
+  // leaf-ordered copies of the (set-up) primitives for the compact tree: source ids + the output table, both in the arena
+  const int32_t* d_src = nullptr;
+  const LPrim* d_lp = nullptr;
+  if (have_cn) {
+    arena.add(lp_src, &d_src);
+    arena.reserve(nullptr, lp_src.size() * sizeof(LPrim), reinterpret_cast<const void**>(&d_lp));
+  }
+  SCK(arena.commit(s));
 #undef SCK
 
-  if (d->n_tri > 0) {
-    k_setup_tris<<<(unsigned)((d->n_tri + 255) / 256), 256, 0, dev->stream>>>(const_cast<Tri*>(s->sc.tris), (int)d->n_tri);
-    cudaError_t e = cudaStreamSynchronize(dev->stream);
-    if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("k_setup_tris: ") + cudaGetErrorString(e)); }
-  }
-  if (s->sc.cnodes && !lp_src.empty()) {       // leaf-ordered copies of the (set-up) primitives
-    const int32_t* d_src = nullptr;
-    srt_status rc2 = upload(s, lp_src, &d_src);
-    void* lp = nullptr;
-    if (!rc2) {
-      cudaError_t e = cudaMalloc(&lp, lp_src.size() * sizeof(LPrim));
-      if (e != cudaSuccess) { cudaGetLastError(); rc2 = fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
-    }
-    if (rc2) { srt_scene_destroy(s); return rc2; }
-    s->buffers.push_back(lp);
-    s->bytes += (int64_t)(lp_src.size() * sizeof(LPrim));
-    k_build_lprims<<<(unsigned)((lp_src.size() + 255) / 256), 256, 0, dev->stream>>>(s->sc, d_src, (int)lp_src.size(), static_cast<LPrim*>(lp));
-    cudaError_t e = cudaStreamSynchronize(dev->stream);
-    if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("k_build_lprims: ") + cudaGetErrorString(e)); }
-    s->sc.lprims = static_cast<const LPrim*>(lp);
+  // set-up kernels behind the copy, one synchronisation for the whole scene
+  if (d->n_tri > 0) k_setup_tris<<<(unsigned)((d->n_tri + 255) / 256), 256, 0, dev->stream>>>(const_cast<Tri*>(s->sc.tris), (int)d->n_tri);
+  if (have_cn) {
+    s->sc.lprims = d_lp;
+    k_build_lprims<<<(unsigned)((lp_src.size() + 255) / 256), 256, 0, dev->stream>>>(s->sc, d_src, (int)lp_src.size(), const_cast<LPrim*>(d_lp));
   } else {
     s->sc.cnodes = nullptr;
   }
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(dev->stream);
+  if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("scene set-up: ") + cudaGetErrorString(e)); }
   *out = s;
   return SRT_OK;
 } catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }

@@ -38,7 +38,11 @@
 namespace srt {
 
 #define X2_DONE (-1)                 /* lane state: the walk is finished                                     */
-/* lane state <= -2: stopped on leaf node (-2 - state);  >= 0: walking (FMT 32: byte offset of the node, FMT 16: node index) */
+/* lane state <= -2: stopped on a leaf, code = -2 - state = leaf node | (leaf holds a sphere) << X2_KIND_SHIFT;
+   >= 0: walking (FMT 32: byte offset of the node, FMT 16: node index) */
+#define X2_KIND_SHIFT(FMT) ((FMT) == 32 ? 24 : 14)
+#define X2_MAX_NODES(FMT) ((FMT) == 32 ? (1 << 24) - 1 : 16382)   /* FMT 16: -2 - (16382 | 1 << 14) = -32768 still fits 16 bits */
+#define X2_SPH_PARK 64               /* entries of a warp's sphere-leaf list (it never holds more than 63)  */
 
 struct Aux2 { float idx, idy, idz, oidx, oidy, oidz, nMs; };
 
@@ -83,7 +87,9 @@ __device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes
   const bool inner = w7 == NODE_INNER;
   const int scale = FMT == 32 ? 16 : 1;
   const int nxt = k + 1 < n ? (k + 1) * scale : X2_DONE;
-  const int link_hit = inner ? nxt : -2 - k;
+  // a leaf's stop code carries whether it holds a sphere (its parked ray then waits in the sphere list)
+  const bool has_sph = !inner && (w6 >= sc.n_tri || w7 >= sc.n_tri);
+  const int link_hit = inner ? nxt : -2 - (k | (has_sph ? 1 << X2_KIND_SHIFT(FMT) : 0));
   const int link_miss = inner ? (w6 < n ? w6 * scale : X2_DONE) : nxt;
   const float* c = sc.x2_centre;
   const float lx = x2_lo(lo.x, c[0]), ly = x2_lo(lo.y, c[1]), lz = x2_lo(lo.z, c[2]);
@@ -122,13 +128,44 @@ __device__ __forceinline__ void walk2_step(uint32_t nodes_s, uint32_t hi_off, co
   }
 }
 
-// the leaf a parked ray waits on, with the reference's arithmetic: aabb::hit on the true box, then its primitives in order
-template <bool COUNT>
+// aabb::hit / triangle::hit as in srt_core.cuh (same operations, same order, same NaN behaviour) without the early returns:
+// in a leaf phase some lane nearly always needs the last stage, so the returns only cost branches.
+__device__ __forceinline__ bool box_hit_exact_nb(const float4& lo, const float4& hi, const Ray& r, float tMin, float tMax) {
+  float a, b;
+  a = (lo.x - r.o.x) / r.d.x; b = (lo.w - r.o.x) / r.d.x;
+  tMin = fmaxf(fminf(a, b), tMin); tMax = fminf(fmaxf(a, b), tMax);
+  bool miss = tMax <= tMin;
+  a = (lo.y - r.o.y) / r.d.y; b = (hi.x - r.o.y) / r.d.y;
+  tMin = fmaxf(fminf(a, b), tMin); tMax = fminf(fmaxf(a, b), tMax);
+  miss = miss || tMax <= tMin;
+  a = (lo.z - r.o.z) / r.d.z; b = (hi.y - r.o.z) / r.d.z;
+  tMin = fmaxf(fminf(a, b), tMin); tMax = fminf(fmaxf(a, b), tMax);
+  return !(miss || tMax <= tMin);
+}
+__device__ __forceinline__ bool tri_hit_nb(const Tri* __restrict__ tris, int i, const Ray& r, float tMin, float& tOut) {
+  const float4 A = __ldg(&tris[i].a), B = __ldg(&tris[i].b), C = __ldg(&tris[i].c);
+  const float dd = __ldg(&tris[i].d.x);
+  const V3 N = mk(A.w, B.w, C.w);
+  const float NdotDir = dot(N, r.d);
+  // model.h:119,122,128: the plane stage still returns - half of the candidates are back faces
+  if (fabsf(NdotDir) < FLT_EPSILON || NdotDir > 0) return false;
+  const float t = -(dot(N, r.o) + dd) / NdotDir;
+  if (t < tMin) return false;
+  const V3 v0 = mk(A.x, A.y, A.z), v1 = mk(B.x, B.y, B.z), v2 = mk(C.x, C.y, C.z);
+  const V3 p = mk(r.o.x + t * r.d.x, r.o.y + t * r.d.y, r.o.z + t * r.d.z);
+  const float e0 = dot(N, cross(v1 - v0, p - v0)), e1 = dot(N, cross(v2 - v1, p - v1)), e2 = dot(N, cross(v0 - v2, p - v2));
+  tOut = t;
+  return !(e0 < 0) && !(e1 < 0) && !(e2 < 0);           // model.h:136-154
+}
+
+// the leaf a parked ray waits on, with the reference's arithmetic: aabb::hit on the true box, then its primitives in order.
+// SPH = false: the leaf holds triangles only (the warp's triangle list) - no sphere code in that phase at all.
+template <bool COUNT, bool SPH>
 __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r, float& tCur, int& prim, Counters& cnt) {
   float4 lo, hi;
   load_node_soa<false>(sc.nodes, 0u, 0u, node, lo, hi);
   if (COUNT) ++cnt.exact;
-  if (!box_hit_exact(lo, hi, r, 0.001f, tCur)) return;
+  if (!box_hit_exact_nb(lo, hi, r, 0.001f, tCur)) return;
   const int pa = __float_as_int(hi.z), pb = __float_as_int(hi.w);
 #pragma unroll 1
   for (int k = 0; k < 2; k++) {
@@ -136,25 +173,60 @@ __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r,
     if (p < 0) break;
     if (COUNT) { ++cnt.leaves; if (p >= sc.n_tri) ++cnt.sph_leaves; }
     float t;
-    const bool acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
+    bool acc;
+    if (SPH) acc = p < sc.n_tri ? tri_hit_nb(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
+    else acc = tri_hit_nb(sc.tris, p, r, 0.001f, t);
     if (acc) { tCur = t; prim = p; }
   }
 }
 
+// One leaf phase of a warp: the top `take` <= 32 entries of `list` (count `cnt_list`), one per lane; rays whose walk goes on
+// are pushed on the ready stack (entries ready_top[-1 - k]).
+template <bool COUNT, bool SPH>
+__device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& pool, uint4* list, int& n_list, uint4* ready_top, int& r,
+                                              int lane, int n, int step_scale, Counters& cnt) {
+  const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1u;
+  const int take = n_list < 32 ? n_list : 32;
+  bool push = false;
+  uint4 res = make_uint4(0, 0, 0, 0);
+  if (lane < take) {
+    const uint4 q = list[n_list - take + lane];
+    const float4 d = __ldg(&pool.ray_d[q.x]), o = __ldg(&pool.ray_o[q.x]);
+    Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
+    float tc = __uint_as_float(q.z);
+    int pr = (int)q.w;
+    x2_leaf<COUNT, SPH>(sc, (int)q.y, ry, tc, pr, cnt);
+    const int nxt = (int)q.y + 1;
+    if (nxt >= n) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));          // the leaf was the last node: the walk is over
+    else { push = true; res = make_uint4(q.x, (unsigned)(nxt * step_scale), __float_as_uint(tc), (unsigned)pr); }
+  }
+  n_list -= take;
+  const unsigned mp = __ballot_sync(FULL, push);      // (also orders the reads above before the writes below)
+  if (push) ready_top[-1 - r - __popc(mp & below)] = res;
+  r += __popc(mp);
+  __syncwarp();
+}
+
 #ifndef SRT_X2_REPS
-#define SRT_X2_REPS 2
+#define SRT_X2_REPS 4             /* box tests per vote: 4 measured 3.6 % ahead of 2 (B200, config 4) */
 #endif
 #ifndef SRT_X2_DEFAULT_FMT
 #define SRT_X2_DEFAULT_FMT 32     /* node bytes plan_render asks for first: 16, 32, or 0 = keep k_wf_extend */
 #endif
 #ifndef SRT_X2_DEFAULT_TH
-#define SRT_X2_DEFAULT_TH 16      /* lanes that must still be walking for the walk loop to go on */
+#define SRT_X2_DEFAULT_TH 8       /* lanes that must still be walking for the walk loop to go on (B200 sweep: 8 < 12 < 16 < 24) */
 #endif
+#define SRT_X2_PARK 160           /* entries per warp: X2_SPH_PARK + 96 */
 
 // Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint4 entries per warp:
-// pending entries (slot, leaf node, tCur, prim) grow from index 0, ready entries (slot, next state, tCur, prim) from the top.
-// A warp never holds more than 63 parked rays (fresh rays are fetched only when no ready one is left and fewer than 32 are
-// pending), so park = 64 always suffices.
+//   [0, 64)          rays waiting on a leaf that holds a sphere      (slot, leaf node, tCur, prim), count ps
+//   [64, 64 + pt)    rays waiting on a leaf of triangles only        (same), count pt
+//   [park - r, park) rays whose leaf is done and whose walk goes on  (slot, next state, tCur, prim)
+// Two pending lists, because a phase costs what its slowest lane costs: a triangle phase runs no sphere code, a sphere
+// phase (the 4 spheres of configs 3/4 are tested 1.75 times per segment - their boxes span the scene) runs triangle code
+// only for leaves that mix both.
+// Bound on parked rays: fresh rays are fetched only when no ready entry is left, after both lists were cut below 32, so a
+// warp holds at most 32 + 31 + 31 = 94 rays; ps <= 63, pt + r <= 94  ->  park = 64 + 96.
 template <bool COUNT, int FMT, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
                                                           unsigned long long* counters) {
@@ -163,7 +235,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
   for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2);
   const int node_u4 = FMT == 32 ? 2 * n : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint4* s_park = smem_x2 + node_u4 + warp * park;
+  uint4* s_sph = smem_x2 + node_u4 + warp * park;
+  uint4* s_tri = s_sph + X2_SPH_PARK;
+  uint4* s_top = s_sph + park;                      // ready entries: s_top[-1 - k]
   const uint32_t nodes_s = (uint32_t)__cvta_generic_to_shared(smem_x2);
   const uint32_t hi_off = (uint32_t)n * 16u;
   __syncthreads();
@@ -171,13 +245,14 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
   const float INF = __int_as_float(0x7f800000);
   const int root = n > 0 ? 0 : X2_DONE;
   const int step_scale = FMT == 32 ? 16 : 1;
+  constexpr int KSH = X2_KIND_SHIFT(FMT);
   Counters cnt = {0, 0, 0, 0, 0};
   if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // set anew by the next shade pass
 
   Aux2 x = {0, 0, 0, 0, 0, 0, 0};
   int i = X2_DONE, slot = -1, prim = -1;
   float tCur = INF;
-  int p = 0, r = 0;                 // warp-uniform: pending entries [0, p), ready entries [park - r, park)
+  int pt = 0, ps = 0, r = 0;        // warp-uniform list counts
   bool pool_dry = false;            // warp-uniform: the wave's rays are all handed out
 
   for (;;) {
@@ -185,38 +260,31 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     const bool has = slot >= 0;
     const bool stp = has && i <= -2;
     if (has && i == X2_DONE) { pool.hit[slot] = make_int2(prim, __float_as_int(tCur)); slot = -1; }
-    const unsigned ms = __ballot_sync(FULL, stp);
+    const int code = -2 - i;
+    const bool stp_s = stp && (code >> KSH) != 0;
+    const unsigned ms = __ballot_sync(FULL, stp), mss = __ballot_sync(FULL, stp_s);
     if (stp) {
-      s_park[p + __popc(ms & below)] = make_uint4((unsigned)slot, (unsigned)(-2 - i), __float_as_uint(tCur), (unsigned)prim);
+      const uint4 e = make_uint4((unsigned)slot, (unsigned)(code & ((1 << KSH) - 1)), __float_as_uint(tCur), (unsigned)prim);
+      if (stp_s) s_sph[ps + __popc(mss & below)] = e;
+      else s_tri[pt + __popc(ms & ~mss & below)] = e;
       slot = -1; i = X2_DONE;
     }
-    p += __popc(ms);
+    ps += __popc(mss); pt += __popc(ms & ~mss);
     __syncwarp();
-    // ---- B. leaf phase: 32 parked rays, one per lane (fewer only when nothing else can fill the lanes)
-    unsigned m_empty = __ballot_sync(FULL, slot < 0);
-    if (p >= 32 || (p > 0 && pool_dry && r < __popc(m_empty))) {
-      const int take = p < 32 ? p : 32;
-      bool push = false;
-      uint4 res = make_uint4(0, 0, 0, 0);
-      if (lane < take) {
-        const uint4 q = s_park[p - take + lane];
-        const float4 d = __ldg(&pool.ray_d[q.x]), o = __ldg(&pool.ray_o[q.x]);
-        Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
-        float tc = __uint_as_float(q.z);
-        int pr = (int)q.w;
-        x2_leaf<COUNT>(sc, (int)q.y, ry, tc, pr, cnt);
-        const int nxt = (int)q.y + 1;
-        if (nxt >= n) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));          // the leaf was the last node: the walk is over
-        else { push = true; res = make_uint4(q.x, (unsigned)(nxt * step_scale), __float_as_uint(tc), (unsigned)pr); }
-      }
-      p -= take;
-      const unsigned mp = __ballot_sync(FULL, push);      // (also orders the reads above before the writes below)
-      if (push) s_park[park - r - 1 - __popc(mp & below)] = res;
-      r += __popc(mp);
-      __syncwarp();
+    // ---- B. leaf phases: 32 parked rays of one list, one per lane (fewer only when nothing else can fill the lanes)
+    // The end of a wave (no ray left to fetch, none ready): a phase for every idle lane would test one or two leaves at a
+    // time, each behind three dependent global loads (64 such phases per warp measured: 10 % of the launch).  Instead the
+    // walkers run on until every lane has stopped, and one phase per list serves them all.
+    const bool drain = pool_dry && r == 0;
+    {
+      const bool idle = drain && __ballot_sync(FULL, slot < 0) == FULL;
+      if (pt >= 32 || (pt > 0 && idle))
+        x2_leaf_phase<COUNT, false>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
+      if (ps >= 32 || (ps > 0 && idle))
+        x2_leaf_phase<COUNT, true>(sc, pool, s_sph, ps, s_top, r, lane, n, step_scale, cnt);
     }
     // ---- C. empty lanes take a ready ray, else the next ray of the wave (one atomic per warp)
-    m_empty = __ballot_sync(FULL, slot < 0);
+    const unsigned m_empty = __ballot_sync(FULL, slot < 0);
     if (m_empty) {
       const int n_empty = __popc(m_empty), q = __popc(m_empty & below);
       const int take = r < n_empty ? r : n_empty;
@@ -233,7 +301,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
         int link = root;
         bool is_fresh = false;
         if (q < take) {
-          const uint4 e = s_park[park - r + q];
+          const uint4 e = s_top[-1 - (r - take + q)];
           mine = (long long)e.x; link = (int)e.y; tCur = __uint_as_float(e.z); prim = (int)e.w;
         } else if (q - take < fresh) {
           const unsigned long long idx = base + (unsigned long long)(q - take);
@@ -259,10 +327,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     const unsigned mW = __ballot_sync(FULL, i >= 0);
     if (!mW) {
       if (__ballot_sync(FULL, slot >= 0)) continue;          // finished / stopped lanes only: serve them
-      if (p == 0 && r == 0 && pool_dry) break;
+      if (pt == 0 && ps == 0 && r == 0 && pool_dry) break;
       continue;
     }
-    const int th = __popc(mW) < th_walk ? __popc(mW) : th_walk;
+    const int th = (pool_dry && r == 0) ? 1 : (__popc(mW) < th_walk ? __popc(mW) : th_walk);   // draining: walk until all have stopped
     do {
 #pragma unroll
       for (int rep = 0; rep < SRT_X2_REPS; rep++)

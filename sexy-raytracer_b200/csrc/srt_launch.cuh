@@ -43,7 +43,18 @@ struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
   int wf_slots, wf_th_walk, wf_shade_chunk; const void* wf_shade;     // variant 2
   int x2_fmt, x2_park;                                                // variant 2 with k_wf_extend2: node bytes (0 = k_wf_extend), entries per warp
+  int fused, path_chunk;                                              // variant 2 as ONE launch of k_wf_path (srt_path.cuh); path ids per atomic
 };
+
+typedef void (*path_fn)(Scene, RenderArgs, PathPool, WfCursors*, float*, int, int, unsigned long long*);
+template <int THREADS>
+path_fn pick_path(bool count, int fmt) {
+  if (count) return fmt == 16 ? k_wf_path<true, 16, THREADS> : k_wf_path<true, 32, THREADS>;
+  return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
+}
+#ifndef SRT_PATH_DEFAULT
+#define SRT_PATH_DEFAULT 0        /* 1: variant 2 runs as k_wf_path whenever k_wf_extend2 would be used and the lists fit */
+#endif
 
 typedef void (*extend2_fn)(Scene, WfPool, WfCursors*, int, int, unsigned long long*);
 template <int THREADS>
@@ -101,14 +112,14 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   const int mode = s->nodes_in_smem ? 0 : compact ? 2 : 1;
   // Tree in shared memory: k_wf_extend2 (conservative walk + parked leaf tests, srt_extend2.cuh) whenever the scene allows
   // it and its nodes + park lists fit; 16-byte nodes first (half the shared-memory wavefronts per step), 32-byte otherwise.
-  plan.x2_fmt = 0; plan.x2_park = 64;
+  plan.x2_fmt = 0; plan.x2_park = SRT_X2_PARK;
   if (mode == 0 && s->sc.x2_ok) {
     int want = SRT_X2_DEFAULT_FMT;
     if (const char* e = tune_env("SRT_WF_X2")) want = atoi(e);
     cudaFuncAttributes fa2{};
     for (int fmt : {want, want == 16 ? 32 : 0}) {
       if (fmt != 16 && fmt != 32) continue;
-      if (fmt == 16 && s->sc.n_nodes > 32000) continue;                     // 16-bit links
+      if (s->sc.n_nodes > X2_MAX_NODES(fmt)) continue;                      // links + the leaf-kind bit of the stop code
       const void* f2 = plan.threads == 1024 ? (const void*)pick_extend2<1024>(dev->counters, fmt)
                        : plan.threads == 768 ? (const void*)pick_extend2<768>(dev->counters, fmt)
                        : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
@@ -119,6 +130,20 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
       if (!wf_env) plan.wf_th_walk = SRT_X2_DEFAULT_TH;
       break;
+    }
+  }
+  // ... and as ONE launch per frame (k_wf_path: the shade step inside the persistent kernel) when its lists fit beside the tree
+  plan.fused = 0; plan.path_chunk = 1024;
+  if (plan.x2_fmt && (plan.threads == 1024 || plan.threads == 512)) {
+    int want = SRT_PATH_DEFAULT;
+    if (const char* e = tune_env("SRT_WF_FUSED")) want = atoi(e);
+    if (want) {
+      const void* fp = plan.threads == 1024 ? (const void*)pick_path<1024>(dev->counters, plan.x2_fmt) : (const void*)pick_path<512>(dev->counters, plan.x2_fmt);
+      cudaFuncAttributes fa3{};
+      const size_t need = (size_t)s->sc.n_nodes * (size_t)plan.x2_fmt + (size_t)(plan.threads / 32) * PATH_WARP_BYTES;
+      if (cudaFuncGetAttributes(&fa3, fp) == cudaSuccess && need + fa3.sharedSizeBytes <= dev->smem_optin && s->sc.n_nodes * 16ll < (1ll << 24)) {
+        plan.fused = 1; plan.fn = fp; plan.smem = need;
+      } else cudaGetLastError();
     }
   }
   if (!plan.x2_fmt) {
@@ -219,7 +244,7 @@ srt_status plan_render(srt_scene* s, const srt_camera* cam, const srt_render_par
 // variant 2: SHADE(+regenerate) / EXTEND waves over the slot pool until the frame's paths are used up
 srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
   srt_device* dev = s->dev;
-  const size_t per_slot = 2 * sizeof(float4) + sizeof(int2) + sizeof(uint2) + 2 * sizeof(float4);
+  const size_t per_slot = 3 * sizeof(float4) + sizeof(int2) + sizeof(uint2);   // ray_o, ray_d, thr | hit, id = 64 bytes
   const size_t N = (size_t)plan.wf_slots;
   if (dev->wf_capacity < N) {
     if (dev->wf.ray_o) { CK(cudaFree(dev->wf.ray_o)); dev->wf.ray_o = nullptr; dev->wf_capacity = 0; }
@@ -241,7 +266,6 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     pool.ray_o = (float4*)b; b += C * sizeof(float4);
     pool.ray_d = (float4*)b; b += C * sizeof(float4);
     pool.thr = (float4*)b;   b += C * sizeof(float4);
-    pool.rad = (float4*)b;   b += C * sizeof(float4);
     pool.hit = (int2*)b;     b += C * sizeof(int2);
     pool.id = (uint2*)b;
     pool.n_slots = (int)N;
@@ -348,6 +372,58 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   return SRT_OK;
 }
 
+// variant 2, fused: one persistent launch traces, shades and regenerates until the frame's paths are used up (srt_path.cuh)
+srt_status run_path(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
+  srt_device* dev = s->dev;
+  const size_t N = (size_t)plan.blocks * (size_t)(plan.threads / 32) * PATH_SLOTS;     // warp-private slots
+  const size_t per_slot = 3 * sizeof(float4) + sizeof(int2) + sizeof(uint2);
+  if (dev->path_capacity < N) {
+    if (dev->d_path) { CK(cudaFree(dev->d_path)); dev->d_path = nullptr; dev->path_capacity = 0; }
+    cudaError_t e = cudaMalloc(&dev->d_path, N * per_slot);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(SRT_ERR_NOMEM, "path slots: " + std::string(cudaGetErrorString(e))); }
+    dev->path_capacity = N;
+  }
+  if (!dev->d_wf_cur) {
+    CK(cudaMalloc(&dev->d_wf_cur, sizeof(WfCursors)));
+    CK(cudaMallocHost(&dev->h_wf_ring, WF_RING * sizeof(WfCursors)));
+    for (int k = 0; k < WF_RING; k++) CK(cudaEventCreateWithFlags(&dev->wf_ev[k], cudaEventDisableTiming));
+    for (int k = 0; k < WF_TRING; k++) for (int q = 0; q < 3; q++) CK(cudaEventCreate(&dev->wf_t[k][q]));
+  }
+  PathPool pool;
+  {
+    char* b = (char*)dev->d_path; const size_t C = dev->path_capacity;
+    pool.ray_o = (float4*)b; b += C * sizeof(float4);
+    pool.ray_d = (float4*)b; b += C * sizeof(float4);
+    pool.thr = (float4*)b;   b += C * sizeof(float4);
+    pool.hit = (int2*)b;     b += C * sizeof(int2);
+    pool.id = (uint2*)b;
+  }
+  // path ids per global atomic: 1024 (32 pixel tiles of one sample index), fewer when the frame is small against the grid
+  const unsigned long long total = (unsigned long long)plan.A.n_tiles * 32ull * (unsigned long long)plan.A.sample_count;
+  const unsigned long long warps = (unsigned long long)plan.blocks * (unsigned long long)(plan.threads / 32);
+  int chunk = (int)std::min<unsigned long long>(1024, std::max<unsigned long long>(32, total / (warps * 4) / 32 * 32));
+  Scene sc = s->sc; RenderArgs A = plan.A; WfCursors* cur = dev->d_wf_cur; unsigned long long* ctr = dev->d_counters;
+  int th_walk = plan.wf_th_walk;
+  void* args[] = {&sc, &A, &pool, &cur, &accum_dev, &th_walk, &chunk, &ctr};
+  CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
+  CK(cudaMemsetAsync(cur, 0, sizeof(WfCursors), dev->stream));
+  CK(cudaEventRecord(dev->ev0, dev->stream));
+  CK(cudaLaunchKernel(plan.fn, dim3(plan.blocks), dim3(plan.threads), args, plan.smem, dev->stream));
+  CK(cudaEventRecord(dev->ev1, dev->stream));
+  unsigned long long h[8];
+  CK(cudaMemcpyAsync(h, dev->d_counters, sizeof h, cudaMemcpyDeviceToHost, dev->stream));
+  CK(cudaStreamSynchronize(dev->stream));
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->paths = h[0]; stats->segments = h[1]; stats->node_visits = h[2]; stats->leaf_tests = h[3];
+    float ms = 0; CK(cudaEventElapsedTime(&ms, dev->ev0, dev->ev1));
+    stats->kernel_ms = ms; stats->launches = 1;
+    stats->extend_ms = ms; stats->shade_ms = 0; stats->extend_launches = 1; stats->variant = 2; stats->extend_kernel = plan.x2_fmt;
+    stats->fused = 1;
+  }
+  return SRT_OK;
+}
+
 srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, srt_stats* stats) {
   srt_device* dev = s->dev;
   if (plan.A.max_bounce <= 0) {     // rayColor returns (0,0,0) before world.hit (main.cpp:36-37): nothing to add, no segment traced
@@ -358,7 +434,7 @@ srt_status run_render(srt_scene* s, const RenderPlan& plan, float* accum_dev, sr
     }
     return SRT_OK;
   }
-  if (plan.variant == 2) return run_wavefront(s, plan, accum_dev, stats);
+  if (plan.variant == 2) return plan.fused ? run_path(s, plan, accum_dev, stats) : run_wavefront(s, plan, accum_dev, stats);
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaEventRecord(dev->ev0, dev->stream));
   if (plan.variant == 3) {

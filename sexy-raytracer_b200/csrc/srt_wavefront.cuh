@@ -9,7 +9,9 @@
 //   k_wf_shade  : main.cpp:44-51 for every slot with all lanes active, then path regeneration
 //                 (main.cpp:204-217): a slot whose path ended adds its radiance to the pixel
 //                 (red.global.add.f32) and takes the next (pixel, sample) of the frame from a global cursor.
-// Path state lives in HBM between the two (SoA, ~190 B of traffic per segment — two orders of magnitude
+// A path's radiance is not carried: every non-zero term thr * emitted / thr * background is added to the pixel
+// (red.global.add.f32) where it arises - a path of configs 1-4 has one such term, so the pixel sum sees the same addends.
+// Path state lives in HBM between the two (SoA, ~150 B of traffic per segment — two orders of magnitude
 // below what 6.5 TB/s allows at this path's segment rates).  Traversal order per ray, arithmetic and the
 // Philox keying (pixel, sample, bounce) are the megakernel's: frames agree up to fp32 summation order
 // of a pixel's samples.
@@ -32,7 +34,6 @@ struct WfPool {
   int2*   hit;        // (prim, t bits) written by extend
   uint2*  id;         // (pixel, sample)
   float4* thr;        // (throughput.xyz, bounce as int bits; bounce < 0 = slot has no path)
-  float4* rad;        // (radiance so far .xyz, -)
   int     n_slots;
   const unsigned* order;   // extend hands out slots order[0], order[1], ... (nullptr: 0, 1, ...) - see k_wf_keys
 };
@@ -299,20 +300,20 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
     bool wrote_ray = false;
     if (in_pool) {
       // all six loads are issued before the first use (a slot without a path reads stale but valid memory)
-      const float4 t4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
+      const float4 t4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k];
       const int2 h = pool.hit[k];
       const uint2 id = pool.id[k];
       bounce = __float_as_int(t4.w);
       if (bounce >= 0) {
         pixel = id.x; sample = id.y;
         r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
-        thr = mk(t4.x, t4.y, t4.z); L = mk(l4.x, l4.y, l4.z);
+        thr = mk(t4.x, t4.y, t4.z); L = mk(0, 0, 0);
         const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
-        if (done) {
+        if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                           // this segment's term (NaN included)
           float* px = accum + (size_t)pixel * 3;
           atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);     // result unused -> red.global.add.f32
-          bounce = -1;
-        } else wrote_ray = true;
+        }
+        if (done) bounce = -1; else wrote_ray = true;
       }
     }
     // regeneration: slots without a path take the next path ids of the frame
@@ -349,7 +350,6 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
         pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
         pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
         pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
-        pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
         if (new_path) pool.id[k] = make_uint2(pixel, sample);
       } else {                                    // no path: extend skips the slot, the next shade pass retries
         pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
@@ -388,95 +388,104 @@ template <bool COUNT>
 __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
                                                    unsigned long long* counters) {
   constexpr int CH = 512;
-  __shared__ unsigned short s_hit[CH], s_free[CH];
-  __shared__ unsigned s_nhit, s_nfree;
+  // lists and their counts are double buffered by chunk parity: three barriers per chunk instead of five
+  __shared__ unsigned short s_hit[2][CH], s_free[2][CH];
+  __shared__ unsigned s_nhit[2], s_nfree[2];
   __shared__ unsigned long long s_base;
   __shared__ unsigned long long s_stat[3];
   const int lane = threadIdx.x & 31;
-  const unsigned FULL = 0xffffffffu;
+  const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1;
   if (blockIdx.x == 0 && threadIdx.x == 0) cur->ray = 0;    // the next extend wave starts at slot 0
   if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+  if (threadIdx.x < 2) { s_nhit[threadIdx.x] = 0; s_nfree[threadIdx.x] = 0; }
   const unsigned long long per_sample = (unsigned long long)A.n_tiles * 32ull;
   const unsigned long long total = per_sample * (unsigned long long)A.sample_count;
   Counters cnt = {0, 0, 0, 0, 0};
   unsigned n_new = 0, n_seg = 0;
+  __syncthreads();
 
-  for (int chunk = blockIdx.x; chunk * CH < pool.n_slots; chunk += gridDim.x) {
+  int buf = 0;
+  for (int chunk = blockIdx.x; chunk * CH < pool.n_slots; chunk += gridDim.x, buf ^= 1) {
     const int base = chunk * CH;
-    if (threadIdx.x == 0) { s_nhit = 0; s_nfree = 0; }
 #if SRT_SHADE_PREFETCH
-    {   // the block's next chunk: pull its 6 x 512 records towards the L2 while this chunk is served (they stream from HBM)
+    {   // the block's next chunk: pull its 5 x 512 records towards the L2 while this chunk is served (they stream from HBM)
       const long long nb = (long long)(chunk + (int)gridDim.x) * CH;
       if (nb + CH <= (long long)pool.n_slots) {
-        const int a = threadIdx.x >> 6, line = threadIdx.x & 63;               // four 16-byte arrays x 64 lines of 128 bytes
-        const float4* p16 = a == 0 ? pool.thr : a == 1 ? pool.ray_o : a == 2 ? pool.ray_d : pool.rad;
-        asm volatile("prefetch.global.L2 [%0];" :: "l"(p16 + nb + line * 8));
-        if (threadIdx.x < 64) {                                                // two 8-byte arrays x 32 lines
-          const int l8 = threadIdx.x & 31;
-          const void* p8 = threadIdx.x < 32 ? (const void*)(pool.hit + nb + l8 * 16) : (const void*)(pool.id + nb + l8 * 16);
+        const int a = threadIdx.x >> 6, line = threadIdx.x & 63;               // three 16-byte arrays x 64 lines of 128 bytes
+        if (a < 3) {
+          const float4* p16 = a == 0 ? pool.thr : a == 1 ? pool.ray_o : pool.ray_d;
+          asm volatile("prefetch.global.L2 [%0];" :: "l"(p16 + nb + line * 8));
+        } else {                                                               // two 8-byte arrays x 32 lines
+          const int l8 = line & 31;
+          const void* p8 = line < 32 ? (const void*)(pool.hit + nb + l8 * 16) : (const void*)(pool.id + nb + l8 * 16);
           asm volatile("prefetch.global.L2 [%0];" :: "l"(p8));
         }
       }
     }
 #endif
-    __syncthreads();
-    // ---- pass 0: classify (two slots per thread)
+    // ---- pass 0: classify (two slots per thread, all loads first)
+    float4 t4[2]; int2 h[2]; uint32_t pix[2];
 #pragma unroll
     for (int q = 0; q < 2; q++) {
-      const int j = q * 256 + threadIdx.x, k = base + j;
+      const int k = base + q * 256 + threadIdx.x;
+      t4[q] = make_float4(0, 0, 0, __int_as_float(-2)); h[q] = make_int2(-1, 0); pix[q] = 0;
+      if (k < pool.n_slots) { t4[q] = pool.thr[k]; h[q] = pool.hit[k]; pix[q] = pool.id[k].x; }
+    }
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const int j = q * 256 + threadIdx.x;
+      const int bounce = __float_as_int(t4[q].w);
       bool is_hit = false, is_free = false;
-      if (k < pool.n_slots) {
-        const float4 t4 = pool.thr[k];
-        const int2 h = pool.hit[k];
-        if (__float_as_int(t4.w) < 0) is_free = true;                      // no path in this slot
-        else if (h.x < 0) {                                                // miss -> background, main.cpp:39-40
-          const float4 l4 = pool.rad[k];
-          const uint32_t pixel = pool.id[k].x;
-          float* px = accum + (size_t)pixel * 3;
-          atomicAdd(px, l4.x + t4.x * A.bg[0]); atomicAdd(px + 1, l4.y + t4.y * A.bg[1]); atomicAdd(px + 2, l4.z + t4.z * A.bg[2]);
+      if (bounce == -1) is_free = true;                                    // no path in this slot (-2: beyond the pool)
+      else if (bounce >= 0) {
+        if (h[q].x < 0) {                                                  // miss -> background, main.cpp:39-40
+          float* px = accum + (size_t)pix[q] * 3;
+          atomicAdd(px, t4[q].x * A.bg[0]); atomicAdd(px + 1, t4[q].y * A.bg[1]); atomicAdd(px + 2, t4[q].z * A.bg[2]);
           is_free = true;
         } else is_hit = true;
       }
       const unsigned mh = __ballot_sync(FULL, is_hit), mf = __ballot_sync(FULL, is_free);
       unsigned bh = 0, bf = 0;
-      if (lane == 0) { if (mh) bh = atomicAdd(&s_nhit, __popc(mh)); if (mf) bf = atomicAdd(&s_nfree, __popc(mf)); }
+      if (lane == 0) { if (mh) bh = atomicAdd(&s_nhit[buf], __popc(mh)); if (mf) bf = atomicAdd(&s_nfree[buf], __popc(mf)); }
       bh = __shfl_sync(FULL, bh, 0); bf = __shfl_sync(FULL, bf, 0);
-      const unsigned below = (1u << lane) - 1;
-      if (is_hit) s_hit[bh + __popc(mh & below)] = (unsigned short)j;
-      if (is_free) s_free[bf + __popc(mf & below)] = (unsigned short)j;
+      if (is_hit) s_hit[buf][bh + __popc(mh & below)] = (unsigned short)j;
+      if (is_free) s_free[buf][bf + __popc(mf & below)] = (unsigned short)j;
     }
     __syncthreads();
     // ---- pass 1: shade the hits
-    const unsigned n_hit = s_nhit;
+    const unsigned n_hit = s_nhit[buf];
     for (unsigned t = threadIdx.x; t < n_hit; t += 256) {
-      const int j = s_hit[t], k = base + j;
-      const float4 t4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k], l4 = pool.rad[k];
-      const int2 h = pool.hit[k];
+      const int j = s_hit[buf][t], k = base + j;
+      const float4 th4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k];
+      const int2 hh = pool.hit[k];
       const uint2 id = pool.id[k];
-      int bounce = __float_as_int(t4.w);
+      int bounce = __float_as_int(th4.w);
       Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
-      V3 thr = mk(t4.x, t4.y, t4.z), L = mk(l4.x, l4.y, l4.z);
-      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
-      if (done) {
+      V3 thr = mk(th4.x, th4.y, th4.z), L = mk(0, 0, 0);
+      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
+      if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                      // this segment's emitted term (NaN included)
         float* px = accum + (size_t)id.x * 3;
         atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
-        s_free[atomicAdd(&s_nfree, 1u)] = (unsigned short)j;
-      } else {
+      }
+      if (done) s_free[buf][atomicAdd(&s_nfree[buf], 1u)] = (unsigned short)j;
+      else {
         pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
         pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
         pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
-        pool.rad[k] = make_float4(L.x, L.y, L.z, 0.0f);
         ++n_seg;
       }
     }
     __syncthreads();
     // ---- pass 2: regenerate
-    const unsigned n_free = s_nfree;
-    if (threadIdx.x == 0) s_base = n_free ? atomicAdd(&cur->path, (unsigned long long)n_free) : total;
+    const unsigned n_free = s_nfree[buf];
+    if (threadIdx.x == 0) {
+      s_base = n_free ? atomicAdd(&cur->path, (unsigned long long)n_free) : total;
+      s_nhit[buf ^ 1] = 0; s_nfree[buf ^ 1] = 0;     // the next chunk's counts (its lists were last read a chunk ago)
+    }
     __syncthreads();
     const unsigned long long pbase = s_base;
     for (unsigned t = threadIdx.x; t < n_free; t += 256) {
-      const int k = base + s_free[t];
+      const int k = base + s_free[buf][t];
       const unsigned long long mine = pbase + t;
       bool made = false;
       if (mine < total) {
@@ -490,7 +499,6 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
           pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
           pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
           pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
-          pool.rad[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
           pool.id[k] = make_uint2(pixel, sample);
           made = true; ++n_new; ++n_seg;
         }
@@ -500,7 +508,8 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
         pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
       }
     }
-    __syncthreads();                                // the lists are reused by the next chunk
+    // no barrier here: the next chunk fills the other pair of lists, and s_base is not written again before every thread
+    // has passed that chunk's second barrier
   }
   unsigned long long v0 = n_new, v1 = n_seg, v2 = cnt.tri_hits;
   for (int o = 16; o > 0; o >>= 1) {

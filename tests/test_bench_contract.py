@@ -55,3 +55,15 @@ def test_b200_arm_prints_one_json_line():
     e = d["e2e"]
     assert e["value"] > 0 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0
     assert d["cpu_baseline"]["value"] > 0 and d["clocks"]["reasons"] is not None
+
+
+@pytest.mark.gpu
+def test_group_backend_prints_the_same_frame():
+    """bench.py --backend group: the frame through srt_render_group equals the frame of the per-rank route (same Philox keys;
+    on one GPU the same launches - CRC identical)."""
+    a = _run("--config", "c1", "--steps", "1", "--warmup", "3", "--no-cpu")
+    b = _run("--config", "c1", "--steps", "1", "--warmup", "3", "--backend", "group", "--gpus", "1")
+    assert BASE_KEYS | {"gpu_launches", "clocks", "backend"} <= set(b) and b["backend"] == "group"
+    assert b["value"] > 0 and b["e2e"]["value"] > 0 and b["gpu_launches"] > 0
+    assert b["segments_per_step"] == a["segments_per_step"]
+    assert abs(b["sum_total"] - a["sum_total"]) <= 1e-5 * abs(a["sum_total"])

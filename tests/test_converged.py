@@ -27,6 +27,15 @@ from conftest import GOLDEN, psnr_u8
 Q = (0.5, 0.9, 0.99)
 
 
+def report(msg):
+    """the measured numbers of a run: printed, and appended to $SRT_TEST_REPORT when set (DESIGN.md section 3 quotes them)"""
+    print(msg)
+    path = os.environ.get("SRT_TEST_REPORT")
+    if path:
+        with open(path, "a") as f:
+            f.write(msg + "\n")
+
+
 def load(name):
     g = np.load(os.path.join(GOLDEN, name + "_image.npz"))
     H, W = (int(x) for x in g["shape"])
@@ -88,7 +97,7 @@ def test_config3_1000spp_vs_reference(variant, dev_scenes, scenes):
     got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=4, seed=9, variant=variant))
     assert st.paths == W * H * spp
     pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.01, 1.25, -0.5)
-    print("config 3 @1000 spp variant %d: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev q50/q90/q99 %s (A/B %s)" % (st.variant, pa, pb, floor, qg, qab))
+    report("config 3 @1000 spp variant %d: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev q50/q90/q99 %s (A/B %s)" % (st.variant, pa, pb, floor, qg, qab))
 
 
 @pytest.mark.gpu
@@ -99,7 +108,7 @@ def test_config4_720p_256spp_vs_reference(dev_scenes, scenes):
     assert (W, H, int(g["depth"])) == (1280, 720, 4)
     got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=4, seed=9))
     pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.02, 1.25, -0.5)
-    print("720p @%d spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (spp, pa, pb, floor, qg, qab))
+    report("720p @%d spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (spp, pa, pb, floor, qg, qab))
 
 
 @pytest.mark.gpu
@@ -110,7 +119,7 @@ def test_config4_5000spp_vs_reference_spread(dev_scenes, scenes):
     got, rgba, st = dev_scenes["c3_masterchief"].render(s.render_params(width=W, height=H, spp=5000, max_bounce=4, seed=2026))
     assert st.paths == W * H * 5000 and st.variant == 2
     pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, 5000, 0.02, 0.75, 2.0)
-    print("720p @5000 spp: PSNR %.2f / %.2f dB vs 256-spp references, their floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
+    report("720p @5000 spp: PSNR %.2f / %.2f dB vs 256-spp references, their floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
 
 
 @pytest.mark.gpu
@@ -122,7 +131,7 @@ def test_config2_full_size_vs_reference(dev_scenes, scenes):
     got, rgba, st = dev_scenes["c2_cube"].render(s.render_params(width=W, height=H, spp=spp, max_bounce=8, seed=9))
     # a small light in a large dark room: 64 spp is far from converged (A/B floor 17.5 dB), the spread test carries the weight
     pa, pb, floor, qg, qab = check_frame(got, rgba, st, g, H, W, ok, ra, rb, spp, 0.05, 1.25, -0.5)
-    print("config 2 @64 spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
+    report("config 2 @64 spp: PSNR %.2f / %.2f dB, floor %.2f dB; tile dev %s (A/B %s)" % (pa, pb, floor, qg, qab))
 
 
 def test_port_tile_means_vs_converged_golden(scenes, port):

@@ -192,6 +192,66 @@ def test_wavefront_frame_with_extend2(name, x2, device, dev_scenes, scenes):
     assert (np.abs(ra.astype(int) - rb.astype(int)) <= 1).all()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("x2", [16, 32])
+def test_fused_path_kernel_frames(name, x2, device, dev_scenes, scenes):
+    """k_wf_path (extend + shade + regenerate in ONE persistent launch, srt_path.cuh) traces the same paths as the flat
+    megakernel: same path and segment counts, per-pixel sums equal up to fp32 summation order, RGBA8 within 1."""
+    from test_gpu_parity import SMALL
+    s = scenes[name]
+    W, H, spp = SMALL[name]
+    kw = dict(width=W, height=H, spp=spp, seed=11)
+    a, ra, sa = dev_scenes[name].render(s.render_params(variant=1, **kw))
+    with env(SRT_WF_X2=x2, SRT_WF_FUSED=1):
+        b, rb, sb = dev_scenes[name].render(s.render_params(variant=2, **kw))
+        with env(SRT_WF="4096,512,12"):
+            c, _, sc_ = dev_scenes[name].render(s.render_params(variant=2, **kw), want_rgba=False)
+    if sb.extend_kernel:                       # (a tree k_wf_extend2 cannot serve keeps the two-kernel wavefront)
+        assert sb.fused == 1 and sb.launches == 1 and sc_.fused == 1
+    assert sa.paths == sb.paths == sc_.paths and sa.segments == sb.segments == sc_.segments
+    fin = np.isfinite(a).all(axis=2)
+    assert (np.isfinite(b).all(axis=2) == fin).all()
+    assert np.abs(a[fin] - b[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max())
+    assert np.abs(a[fin] - c[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max())
+    assert (np.abs(ra.astype(int) - rb.astype(int)) <= 1).all()
+
+
+@pytest.mark.gpu
+def test_fused_path_kernel_odd_sizes_depths_and_counters(device, dev_scenes, scenes):
+    """frames whose width / height are not multiples of the 8x4 tile, one-bounce and deep paths, Russian roulette, a sample
+    window, and the counted build: k_wf_path against the two-kernel wavefront on the same Philox keys"""
+    s = scenes["c3_masterchief"]
+    ds = dev_scenes["c3_masterchief"]
+    cases = [dict(width=37, height=23, spp=9, max_bounce=4), dict(width=130, height=66, spp=3, max_bounce=1),
+             dict(width=64, height=36, spp=16, max_bounce=12, rr_begin=2), dict(width=2, height=2, spp=1, max_bounce=4),
+             dict(width=100, height=56, spp=20, max_bounce=4, sample_begin=7, sample_count=5)]
+    for kw in cases:
+        with env(SRT_WF_FUSED=0):
+            a, _, sa = ds.render(s.render_params(variant=2, seed=5, **kw), want_rgba=False)
+        with env(SRT_WF_FUSED=1):
+            b, _, sb = ds.render(s.render_params(variant=2, seed=5, **kw), want_rgba=False)
+        assert sb.fused == 1 and sa.fused == 0, kw
+        assert sa.paths == sb.paths and sa.segments == sb.segments, kw
+        fin = np.isfinite(a).all(axis=2)
+        assert (np.isfinite(b).all(axis=2) == fin).all()
+        assert np.abs(a[fin] - b[fin]).max() <= 2e-5 * max(1.0, np.abs(a[fin]).max()), kw
+    device.set_counters(True)
+    try:
+        kw = dict(width=160, height=90, spp=8, max_bounce=4, seed=5)
+        with env(SRT_WF_FUSED=0):
+            _, _, sa = ds.render(s.render_params(variant=2, **kw), want_rgba=False, want_sum=False)
+            ca = device.last_counters()
+        with env(SRT_WF_FUSED=1):
+            _, _, sb = ds.render(s.render_params(variant=2, **kw), want_rgba=False, want_sum=False)
+            cb = device.last_counters()
+    finally:
+        device.set_counters(False)
+    assert sa.segments == sb.segments
+    for k in ("leaf_tests", "sphere_leaf_tests", "node_visits", "exact_box_tests", "triangle_hits"):
+        assert ca[k] == cb[k], (k, ca[k], cb[k])
+
+
 def test_extend2_refuses_trees_it_cannot_serve(device, scenes, port):
     """a tree whose boxes are not nested keeps k_wf_extend (plan_wavefront), with the same hits"""
     import copy
