@@ -208,7 +208,7 @@ def test_fused_path_kernel_frames(name, x2, device, dev_scenes, scenes):
         with env(SRT_WF="4096,512,12"):
             c, _, sc_ = dev_scenes[name].render(s.render_params(variant=2, **kw), want_rgba=False)
     if sb.extend_kernel:                       # (a tree k_wf_extend2 cannot serve keeps the two-kernel wavefront)
-        assert sb.fused == 1 and sb.launches == 1 and sc_.fused == 1
+        assert sb.fused == 1 and sb.launches == 2 and sc_.fused == 1      # k_wf_path + k_resolve
     assert sa.paths == sb.paths == sc_.paths and sa.segments == sb.segments == sc_.segments
     fin = np.isfinite(a).all(axis=2)
     assert (np.isfinite(b).all(axis=2) == fin).all()
