@@ -80,7 +80,7 @@ __device__ __forceinline__ unsigned pack_h2(__half a, __half b) { return (unsign
 // One node of the caller's threaded tree (srt_core.cuh: Node) -> the walk's record.  Links: >= 0 next node, X2_DONE, or
 // (-2 - k) = stop on leaf k.
 template <int FMT>
-__device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes) {
+__device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes, bool two_lists = true) {
   const int n = sc.n_nodes;
   const float4 lo = __ldg(&sc.nodes[k].lo), hi = __ldg(&sc.nodes[k].hi);
   const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
@@ -88,7 +88,7 @@ __device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes
   const int scale = FMT == 32 ? 16 : 1;
   const int nxt = k + 1 < n ? (k + 1) * scale : X2_DONE;
   // a leaf's stop code carries whether it holds a sphere (its parked ray then waits in the sphere list)
-  const bool has_sph = !inner && (w6 >= sc.n_tri || w7 >= sc.n_tri);
+  const bool has_sph = two_lists && !inner && (w6 >= sc.n_tri || w7 >= sc.n_tri);
   const int link_hit = inner ? nxt : -2 - (k | (has_sph ? 1 << X2_KIND_SHIFT(FMT) : 0));
   const int link_miss = inner ? (w6 < n ? w6 * scale : X2_DONE) : nxt;
   const float* c = sc.x2_centre;
@@ -180,25 +180,29 @@ __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r,
   }
 }
 
-// One leaf phase of a warp: the top `take` <= 32 entries of `list` (count `cnt_list`), one per lane; rays whose walk goes on
-// are pushed on the ready stack (entries ready_top[-1 - k]).
+// One leaf phase of a warp: the top `take` <= 32 entries of `list` (count `n_list`), one per lane.  An entry is 8 bytes
+// (slot, leaf node): the ray comes from the pool, tCur from pool.hit[slot].y - (prim, t) of the last accept live THERE, written
+// when a leaf accepts, so a parked ray costs 8 bytes of shared memory instead of 16 (the L1 that is left decides how fast the
+// phases' loads come back: 228 KB minus the shared memory in use).  Rays whose walk goes on are pushed on the ready stack
+// (ready_top[-1 - k] = (slot, next state)); a ray whose leaf was the last node is simply done - its hit is already stored.
 template <bool COUNT, bool SPH>
-__device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& pool, uint4* list, int& n_list, uint4* ready_top, int& r,
+__device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& pool, uint2* list, int& n_list, uint2* ready_top, int& r,
                                               int lane, int n, int step_scale, Counters& cnt) {
   const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1u;
   const int take = n_list < 32 ? n_list : 32;
   bool push = false;
-  uint4 res = make_uint4(0, 0, 0, 0);
+  uint2 res = make_uint2(0, 0);
   if (lane < take) {
-    const uint4 q = list[n_list - take + lane];
+    const uint2 q = list[n_list - take + lane];
     const float4 d = __ldg(&pool.ray_d[q.x]), o = __ldg(&pool.ray_o[q.x]);
+    const int2 h = pool.hit[q.x];                                             // (written by this kernel: no __ldg)
     Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
-    float tc = __uint_as_float(q.z);
-    int pr = (int)q.w;
+    float tc = __int_as_float(h.y);
+    int pr = -1;
     x2_leaf<COUNT, SPH>(sc, (int)q.y, ry, tc, pr, cnt);
+    if (pr >= 0) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));           // an accept
     const int nxt = (int)q.y + 1;
-    if (nxt >= n) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));          // the leaf was the last node: the walk is over
-    else { push = true; res = make_uint4(q.x, (unsigned)(nxt * step_scale), __float_as_uint(tc), (unsigned)pr); }
+    if (nxt < n) { push = true; res = make_uint2(q.x, (unsigned)(nxt * step_scale)); }
   }
   n_list -= take;
   const unsigned mp = __ballot_sync(FULL, push);      // (also orders the reads above before the writes below)
@@ -218,26 +222,30 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 #endif
 #define SRT_X2_PARK 160           /* entries per warp: X2_SPH_PARK + 96 */
 
-// Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint4 entries per warp:
-//   [0, 64)          rays waiting on a leaf that holds a sphere      (slot, leaf node, tCur, prim), count ps
+// Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint2 entries per warp:
+//   [0, 64)          rays waiting on a leaf that holds a sphere      (slot, leaf node), count ps
 //   [64, 64 + pt)    rays waiting on a leaf of triangles only        (same), count pt
-//   [park - r, park) rays whose leaf is done and whose walk goes on  (slot, next state, tCur, prim)
+//   [park - r, park) rays whose leaf is done and whose walk goes on  (slot, next state)
 // Two pending lists, because a phase costs what its slowest lane costs: a triangle phase runs no sphere code, a sphere
 // phase (the 4 spheres of configs 3/4 are tested 1.75 times per segment - their boxes span the scene) runs triangle code
-// only for leaves that mix both.
+// only for leaves that mix both.  (th_walk bit 8 set: ONE list for both kinds - A/B runs.)
 // Bound on parked rays: fresh rays are fetched only when no ready entry is left, after both lists were cut below 32, so a
 // warp holds at most 32 + 31 + 31 = 94 rays; ps <= 63, pt + r <= 94  ->  park = 64 + 96.
+// pool.hit[slot] = (prim, t) of the ray's last accepted leaf: (-1, inf) when the ray is fetched, rewritten by every accept;
+// tCur of a parked ray is read back from there.
 template <bool COUNT, int FMT, int THREADS>
-__global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
+__global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk_arg, int park,
                                                           unsigned long long* counters) {
   extern __shared__ uint4 smem_x2[];
   const int n = sc.n_nodes;
-  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2);
+  const bool two_lists = (th_walk_arg & 0x100) == 0;
+  const int th_walk = th_walk_arg & 0xff;
+  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, two_lists);
   const int node_u4 = FMT == 32 ? 2 * n : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint4* s_sph = smem_x2 + node_u4 + warp * park;
-  uint4* s_tri = s_sph + X2_SPH_PARK;
-  uint4* s_top = s_sph + park;                      // ready entries: s_top[-1 - k]
+  uint2* s_sph = reinterpret_cast<uint2*>(smem_x2 + node_u4) + warp * park;
+  uint2* s_tri = s_sph + X2_SPH_PARK;
+  uint2* s_top = s_sph + park;                      // ready entries: s_top[-1 - k]
   const uint32_t nodes_s = (uint32_t)__cvta_generic_to_shared(smem_x2);
   const uint32_t hi_off = (uint32_t)n * 16u;
   __syncthreads();
@@ -250,36 +258,36 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
   if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // set anew by the next shade pass
 
   Aux2 x = {0, 0, 0, 0, 0, 0, 0};
-  int i = X2_DONE, slot = -1, prim = -1;
+  int i = X2_DONE, slot = -1;
   float tCur = INF;
   int pt = 0, ps = 0, r = 0;        // warp-uniform list counts
   bool pool_dry = false;            // warp-uniform: the wave's rays are all handed out
 
   for (;;) {
-    // ---- A. lanes whose walk ended store the hit; lanes stopped on a leaf park their ray
-    const bool has = slot >= 0;
-    const bool stp = has && i <= -2;
-    if (has && i == X2_DONE) { pool.hit[slot] = make_int2(prim, __float_as_int(tCur)); slot = -1; }
+    // ---- A. lanes whose walk ended are free (their hit is in pool.hit already); lanes stopped on a leaf park their ray
+    const bool stp = slot >= 0 && i <= -2;
     const int code = -2 - i;
     const bool stp_s = stp && (code >> KSH) != 0;
     const unsigned ms = __ballot_sync(FULL, stp), mss = __ballot_sync(FULL, stp_s);
     if (stp) {
-      const uint4 e = make_uint4((unsigned)slot, (unsigned)(code & ((1 << KSH) - 1)), __float_as_uint(tCur), (unsigned)prim);
+      const uint2 e = make_uint2((unsigned)slot, (unsigned)(code & ((1 << KSH) - 1)));
       if (stp_s) s_sph[ps + __popc(mss & below)] = e;
       else s_tri[pt + __popc(ms & ~mss & below)] = e;
-      slot = -1; i = X2_DONE;
     }
+    if (i < 0) slot = -1;
+    if (stp) i = X2_DONE;
     ps += __popc(mss); pt += __popc(ms & ~mss);
     __syncwarp();
     // ---- B. leaf phases: 32 parked rays of one list, one per lane (fewer only when nothing else can fill the lanes)
     // The end of a wave (no ray left to fetch, none ready): a phase for every idle lane would test one or two leaves at a
     // time, each behind three dependent global loads (64 such phases per warp measured: 10 % of the launch).  Instead the
     // walkers run on until every lane has stopped, and one phase per list serves them all.
-    const bool drain = pool_dry && r == 0;
     {
-      const bool idle = drain && __ballot_sync(FULL, slot < 0) == FULL;
-      if (pt >= 32 || (pt > 0 && idle))
-        x2_leaf_phase<COUNT, false>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
+      const bool idle = pool_dry && r == 0 && __ballot_sync(FULL, slot < 0) == FULL;
+      if (pt >= 32 || (pt > 0 && idle)) {
+        if (two_lists) x2_leaf_phase<COUNT, false>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
+        else x2_leaf_phase<COUNT, true>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
+      }
       if (ps >= 32 || (ps > 0 && idle))
         x2_leaf_phase<COUNT, true>(sc, pool, s_sph, ps, s_top, r, lane, n, step_scale, cnt);
     }
@@ -301,18 +309,22 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
         int link = root;
         bool is_fresh = false;
         if (q < take) {
-          const uint4 e = s_top[-1 - (r - take + q)];
-          mine = (long long)e.x; link = (int)e.y; tCur = __uint_as_float(e.z); prim = (int)e.w;
+          const uint2 e = s_top[-1 - (r - take + q)];
+          mine = (long long)e.x; link = (int)e.y;
         } else if (q - take < fresh) {
           const unsigned long long idx = base + (unsigned long long)(q - take);
-          if (idx < (unsigned long long)pool.n_slots) { mine = (long long)idx; tCur = INF; prim = -1; is_fresh = true; }
+          if (idx < (unsigned long long)pool.n_slots) { mine = (long long)idx; is_fresh = true; }
         }
         if (mine >= 0) {
           const float4 d = __ldg(&pool.ray_d[mine]), o = __ldg(&pool.ray_o[mine]);
+          if (!is_fresh) tCur = __int_as_float(pool.hit[mine].y);
+          else tCur = INF;
           if (!is_fresh || __float_as_int(d.w) == 1) {
             Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
-            if (make_aux2(ry, sc.x2_centre, x)) { slot = (int)mine; i = link; }
-            else {                                   // only a fresh ray can land here: the exact ordered walk, start to end
+            if (make_aux2(ry, sc.x2_centre, x)) {
+              slot = (int)mine; i = link;
+              if (is_fresh) pool.hit[mine] = make_int2(-1, __float_as_int(INF));
+            } else {                                 // only a fresh ray can land here: the exact ordered walk, start to end
               int pr; float t;
               traverse<COUNT>(sc, sc.nodes, ry, 0.001f, INF, pr, t, &cnt);
               pool.hit[mine] = make_int2(pr, __float_as_int(t));

@@ -41,7 +41,7 @@ static const char* tune_env(const char* name) {
 
 struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
-  int wf_slots, wf_th_walk, wf_shade_chunk; const void* wf_shade;     // variant 2
+  int wf_slots, wf_th_walk, wf_shade_chunk, wf_shade_threads; const void* wf_shade;     // variant 2
   int x2_fmt, x2_park;                                                // variant 2 with k_wf_extend2: node bytes (0 = k_wf_extend), entries per warp
   int fused, path_chunk;                                              // variant 2 as ONE launch of k_wf_path (srt_path.cuh); path ids per atomic
 };
@@ -52,6 +52,9 @@ path_fn pick_path(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_path<true, 16, THREADS> : k_wf_path<true, 32, THREADS>;
   return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
 }
+#ifndef SRT_SHADE2_THREADS
+#define SRT_SHADE2_THREADS 256
+#endif
 #ifndef SRT_PATH_DEFAULT
 #define SRT_PATH_DEFAULT 0        /* 1: variant 2 runs as k_wf_path whenever k_wf_extend2 would be used and the lists fit */
 #endif
@@ -62,9 +65,9 @@ extend2_fn pick_extend2(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_extend2<true, 16, THREADS> : k_wf_extend2<true, 32, THREADS>;
   return fmt == 16 ? k_wf_extend2<false, 16, THREADS> : k_wf_extend2<false, 32, THREADS>;
 }
-// shared memory of k_wf_extend2: the staged nodes + `park` 16-byte entries per warp
+// shared memory of k_wf_extend2: the staged nodes + `park` 8-byte entries per warp
 static size_t x2_smem_bytes(int n_nodes, int fmt, int threads, int park) {
-  return (size_t)n_nodes * (size_t)fmt + (size_t)(threads / 32) * (size_t)park * 16;
+  return (size_t)n_nodes * (size_t)fmt + (size_t)(threads / 32) * (size_t)park * 8;
 }
 
 typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
@@ -156,9 +159,13 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
     const char* sh = tune_env("SRT_WF_SHADE");
     const bool sorted = !(sh && atoi(sh) == 1);
-    plan.wf_shade_chunk = sorted ? 512 : 256;
-    plan.wf_shade = sorted ? (dev->counters ? (const void*)k_wf_shade2<true> : (const void*)k_wf_shade2<false>)
-                           : (dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>);
+    int ts = SRT_SHADE2_THREADS;
+    if (const char* t = tune_env("SRT_WF_SHADE_THREADS")) ts = atoi(t) == 128 ? 128 : 256;
+    plan.wf_shade_threads = sorted ? ts : 256;
+    plan.wf_shade_chunk = sorted ? 2 * ts : 256;
+    if (!sorted) plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
+    else if (ts == 128) plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 128> : (const void*)k_wf_shade2<false, 128>;
+    else plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 256> : (const void*)k_wf_shade2<false, 256>;
   }
   cudaFuncAttributes fa{};
   e = cudaFuncGetAttributes(&fa, plan.fn);
@@ -306,7 +313,7 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   void* extend_args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
   void** extend_args = plan.x2_fmt ? extend_args_x2 : extend_args_v1;
   const unsigned reset_blocks = (unsigned)((N + 255) / 256);
-  unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS;   // persistent: resident CTAs per SM x two rounds
+  unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS * (256 / plan.wf_shade_threads);   // persistent: resident CTAs per SM x two rounds
   {
     const unsigned chunks = (unsigned)((N + plan.wf_shade_chunk - 1) / plan.wf_shade_chunk);
     if (shade_blocks > chunks) shade_blocks = chunks;
@@ -341,7 +348,7 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     }
     cudaEvent_t* t = dev->wf_t[j % WF_TRING];
     CK(cudaEventRecord(t[0], dev->stream));
-    CK(cudaLaunchKernel(plan.wf_shade, dim3(shade_blocks), dim3(256), shade_args, 0, dev->stream));
+    CK(cudaLaunchKernel(plan.wf_shade, dim3(shade_blocks), dim3(plan.wf_shade_threads), shade_args, 0, dev->stream));
     CK(cudaEventRecord(t[1], dev->stream));
     CK(cudaMemcpyAsync(&dev->h_wf_ring[j % WF_RING], cur, sizeof(WfCursors), cudaMemcpyDeviceToHost, dev->stream));
     CK(cudaEventRecord(dev->wf_ev[j % WF_RING], dev->stream));

@@ -384,10 +384,10 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
 //   pass 1  (thread = list item) : shade_segment for the listed hits; paths that end retire
 //   pass 2  (thread = list item) : retired / empty slots take the next path ids of the frame and generate their ray
 // Same arithmetic, same Philox keys; only which thread serves which slot and the order paths are numbered change.
-template <bool COUNT>
-__global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
+template <bool COUNT, int TS>
+__global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shade2(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
                                                    unsigned long long* counters) {
-  constexpr int CH = 512;
+  constexpr int CH = 2 * TS;      // TS = 256 (8 warps meet at the barriers) or 128 (4 warps, twice the CTAs)
   // lists and their counts are double buffered by chunk parity: three barriers per chunk instead of five
   __shared__ unsigned short s_hit[2][CH], s_free[2][CH];
   __shared__ unsigned s_nhit[2], s_nfree[2];
@@ -411,14 +411,13 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
     {   // the block's next chunk: pull its 5 x 512 records towards the L2 while this chunk is served (they stream from HBM)
       const long long nb = (long long)(chunk + (int)gridDim.x) * CH;
       if (nb + CH <= (long long)pool.n_slots) {
-        const int a = threadIdx.x >> 6, line = threadIdx.x & 63;               // three 16-byte arrays x 64 lines of 128 bytes
-        if (a < 3) {
-          const float4* p16 = a == 0 ? pool.thr : a == 1 ? pool.ray_o : pool.ray_d;
-          asm volatile("prefetch.global.L2 [%0];" :: "l"(p16 + nb + line * 8));
-        } else {                                                               // two 8-byte arrays x 32 lines
-          const int l8 = line & 31;
-          const void* p8 = line < 32 ? (const void*)(pool.hit + nb + l8 * 16) : (const void*)(pool.id + nb + l8 * 16);
-          asm volatile("prefetch.global.L2 [%0];" :: "l"(p8));
+        // 128-byte lines of the chunk: three 16-byte arrays x CH/8 lines, two 8-byte arrays x CH/16 lines
+        constexpr int L16 = CH / 8, L8 = CH / 16;
+        for (int t = threadIdx.x; t < 3 * L16 + 2 * L8; t += TS) {
+          const void* p;
+          if (t < 3 * L16) { const int a = t / L16, line = t % L16; p = (a == 0 ? pool.thr : a == 1 ? pool.ray_o : pool.ray_d) + nb + line * 8; }
+          else { const int u = t - 3 * L16, line = u % L8; p = u < L8 ? (const void*)(pool.hit + nb + line * 16) : (const void*)(pool.id + nb + line * 16); }
+          asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
       }
     }
@@ -427,13 +426,13 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
     float4 t4[2]; int2 h[2]; uint32_t pix[2];
 #pragma unroll
     for (int q = 0; q < 2; q++) {
-      const int k = base + q * 256 + threadIdx.x;
+      const int k = base + q * TS + threadIdx.x;
       t4[q] = make_float4(0, 0, 0, __int_as_float(-2)); h[q] = make_int2(-1, 0); pix[q] = 0;
       if (k < pool.n_slots) { t4[q] = pool.thr[k]; h[q] = pool.hit[k]; pix[q] = pool.id[k].x; }
     }
 #pragma unroll
     for (int q = 0; q < 2; q++) {
-      const int j = q * 256 + threadIdx.x;
+      const int j = q * TS + threadIdx.x;
       const int bounce = __float_as_int(t4[q].w);
       bool is_hit = false, is_free = false;
       if (bounce == -1) is_free = true;                                    // no path in this slot (-2: beyond the pool)
@@ -454,7 +453,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
     __syncthreads();
     // ---- pass 1: shade the hits
     const unsigned n_hit = s_nhit[buf];
-    for (unsigned t = threadIdx.x; t < n_hit; t += 256) {
+    for (unsigned t = threadIdx.x; t < n_hit; t += TS) {
       const int j = s_hit[buf][t], k = base + j;
       const float4 th4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k];
       const int2 hh = pool.hit[k];
@@ -484,7 +483,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2(Scene s
     }
     __syncthreads();
     const unsigned long long pbase = s_base;
-    for (unsigned t = threadIdx.x; t < n_free; t += 256) {
+    for (unsigned t = threadIdx.x; t < n_free; t += TS) {
       const int k = base + s_free[buf][t];
       const unsigned long long mine = pbase + t;
       bool made = false;
