@@ -52,6 +52,7 @@ struct srt_device {
   float* d_frame_sum = nullptr; uchar4* d_frame_rgba = nullptr; size_t frame_cap = 0;   // srt_render's device buffers (pixels)
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
+  void* d_wf_ids = nullptr; size_t wf_ids_cap = 0;   // k_wf_shade3: path ids held per shade warp between waves
   void* d_path = nullptr; size_t path_capacity = 0;  // k_wf_path's warp-private path slots (srt_path.cuh)
   void* h_stage = nullptr; size_t h_stage_cap = 0;  // pinned staging of srt_scene_create's arena (scenes up to SCENE_STAGE_MAX bytes)
 };
@@ -61,8 +62,6 @@ static const int WF_TRING = 16;
 struct srt_scene {
   srt_device* dev = nullptr;
   Scene sc{};
-  std::vector<cudaArray_t> arrays;
-  std::vector<cudaTextureObject_t> texobjs;
   std::vector<void*> buffers;
   int64_t bytes = 0;
   int nodes_in_smem = 0;
@@ -120,6 +119,7 @@ void srt_device_destroy(srt_device* d) {
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
   if (d->d_path) cudaFree(d->d_path);
+  if (d->d_wf_ids) cudaFree(d->d_wf_ids);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
   if (d->h_stage) cudaFreeHost(d->h_stage);
   for (int k = 0; k < WF_RING; k++) if (d->wf_ev[k]) cudaEventDestroy(d->wf_ev[k]);
@@ -223,32 +223,45 @@ struct SceneArena {
   size_t total = 0;
   template <typename T>
   void add(const std::vector<T>& v, const T** dptr) { reserve(v.data(), v.size() * sizeof(T), reinterpret_cast<const void**>(dptr)); }
-  void reserve(const void* src, size_t nb, const void** dptr) {
+  size_t reserve(const void* src, size_t nb, const void** dptr) {
     items.push_back({src, nb, total, dptr});
     total += (std::max<size_t>(nb, 16) + 255) & ~(size_t)255;
+    return items.size() - 1;
   }
-  // allocate + enqueue the copies on the device's stream; the sources must stay alive until the stream is synchronised
-  srt_status commit(srt_scene* s) {
-    srt_device* dev = s->dev;
-    void* base = nullptr;
-    cudaError_t e = cudaMalloc(&base, total ? total : 256);
+  char* base = nullptr;
+  // one allocation; every item's device address is known afterwards (tables that hold device pointers are patched by the
+  // caller between alloc and upload)
+  srt_status alloc(srt_scene* s) {
+    void* b = nullptr;
+    cudaError_t e = cudaMalloc(&b, total ? total : 256);
     if (e != cudaSuccess) { cudaGetLastError(); return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
-    s->buffers.push_back(base);
+    s->buffers.push_back(b);
+    base = static_cast<char*>(b);
+    for (const Item& it : items) {
+      if (it.dst) *it.dst = base + it.off;
+      s->bytes += (int64_t)it.nb;
+    }
+    return SRT_OK;
+  }
+  char* ptr(size_t item) const { return base + items[item].off; }
+  // enqueue the copies on the device's stream; the sources must stay alive until the stream is synchronised
+  srt_status upload(srt_scene* s) {
+    srt_device* dev = s->dev;
     const bool staged = total <= SCENE_STAGE_MAX;
     if (staged && dev->h_stage_cap < total) {
       if (dev->h_stage) { CK(cudaFreeHost(dev->h_stage)); dev->h_stage = nullptr; dev->h_stage_cap = 0; }
-      const size_t cap = std::max<size_t>(total, (size_t)4 << 20);
+      const size_t cap = std::max<size_t>(total, (size_t)8 << 20);
       CK(cudaMallocHost(&dev->h_stage, cap));
       dev->h_stage_cap = cap;
     }
+    // staged: one copy covering the items that have a source (reserved-only items at the end of the arena are left out)
+    size_t end = 0;
     for (const Item& it : items) {
-      *it.dst = static_cast<const char*>(base) + it.off;
-      s->bytes += (int64_t)it.nb;
       if (!it.src || !it.nb) continue;
-      if (staged) memcpy(static_cast<char*>(dev->h_stage) + it.off, it.src, it.nb);
-      else CK(cudaMemcpyAsync(static_cast<char*>(base) + it.off, it.src, it.nb, cudaMemcpyHostToDevice, dev->stream));
+      if (staged) { memcpy(static_cast<char*>(dev->h_stage) + it.off, it.src, it.nb); end = std::max(end, it.off + it.nb); }
+      else CK(cudaMemcpyAsync(base + it.off, it.src, it.nb, cudaMemcpyHostToDevice, dev->stream));
     }
-    if (staged && total) CK(cudaMemcpyAsync(base, dev->h_stage, total, cudaMemcpyHostToDevice, dev->stream));
+    if (staged && end) CK(cudaMemcpyAsync(base, dev->h_stage, end, cudaMemcpyHostToDevice, dev->stream));
     return SRT_OK;
   }
 };
@@ -266,8 +279,6 @@ extern "C" {
 void srt_scene_destroy(srt_scene* s) {
   if (!s) return;
   cudaSetDevice(s->dev->gpu);
-  for (auto t : s->texobjs) cudaDestroyTextureObject(t);
-  for (auto a : s->arrays) cudaFreeArray(a);
   for (auto p : s->buffers) cudaFree(p);
   delete s;
 }
@@ -446,36 +457,24 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
 
   // textures: texel (i,j) = (px[0],px[1],px[2],255), px = data + j*bpp*w + i*bpp; bytes past the end read 0
   std::vector<Tex> texs((size_t)d->n_tex);
+  std::vector<std::pair<int, size_t>> images;          // distinct images: (first texture id, arena item of the raw bytes)
+  std::vector<int> tex_image((size_t)d->n_tex, -1);    // texture id -> index into `images`
   for (int i = 0; i < d->n_tex; i++) {
     const srt_texture& t = d->textures[i];
     Tex x; memset(&x, 0, sizeof x);
     x.kind = t.kind; x.r = t.color[0]; x.g = t.color[1]; x.b = t.color[2]; x.even = t.even; x.odd = t.odd;
     x.w = t.width; x.h = t.height; x.missing = (t.kind == SRT_TEX_IMAGE && !t.data) ? 1 : 0;
     if (t.kind == SRT_TEX_IMAGE && t.data) {
+      // the raw bytes go into the arena once per distinct image (the same PNG behind several materials is common); the
+      // device expands them to uchar4 texels (k_expand_texels) - no cudaArray, no texture object, no per-texel host loop
       const size_t n = (size_t)t.width * t.height * t.bpp;
-      std::vector<uchar4> rgba((size_t)t.width * t.height);
-      for (int j = 0; j < t.height; j++)
-        for (int k = 0; k < t.width; k++) {
-          size_t off = (size_t)j * ((size_t)t.bpp * t.width) + (size_t)k * t.bpp;
-          uchar4 p;
-          p.x = off < n ? t.data[off] : 0; p.y = off + 1 < n ? t.data[off + 1] : 0; p.z = off + 2 < n ? t.data[off + 2] : 0; p.w = 255;
-          rgba[(size_t)j * t.width + k] = p;
-        }
-      cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
-      cudaArray_t arr = nullptr;
-      cudaError_t e = cudaMallocArray(&arr, &fmt, t.width, t.height);
-      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaMallocArray: ") + cudaGetErrorString(e)); }
-      s->arrays.push_back(arr);
-      e = cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)t.width * 4, (size_t)t.width * 4, t.height, cudaMemcpyHostToDevice);
-      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaMemcpy2DToArray: ") + cudaGetErrorString(e)); }
-      cudaResourceDesc rd; memset(&rd, 0, sizeof rd); rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
-      cudaTextureDesc td; memset(&td, 0, sizeof td);
-      td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp; td.filterMode = cudaFilterModePoint;
-      td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
-      e = cudaCreateTextureObject(&x.obj, &rd, &td, nullptr);
-      if (e != cudaSuccess) { cudaGetLastError(); srt_scene_destroy(s); return fail(SRT_ERR_CUDA, std::string("cudaCreateTextureObject: ") + cudaGetErrorString(e)); }
-      s->texobjs.push_back(x.obj);
-      s->bytes += (int64_t)rgba.size() * 4;
+      int u = -1;
+      for (size_t q = 0; q < images.size() && u < 0; q++) {
+        const srt_texture& o = d->textures[images[q].first];
+        if (o.width == t.width && o.height == t.height && o.bpp == t.bpp && (o.data == t.data || memcmp(o.data, t.data, n) == 0)) u = (int)q;
+      }
+      if (u < 0) { u = (int)images.size(); images.push_back({i, arena.reserve(t.data, n, nullptr)}); }
+      tex_image[i] = u;
     }
     texs[i] = x;
   }
@@ -506,8 +505,23 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     arena.add(lp_src, &d_src);
     arena.reserve(nullptr, lp_src.size() * sizeof(LPrim), reinterpret_cast<const void**>(&d_lp));
   }
-  SCK(arena.commit(s));
+  std::vector<size_t> texel_item(images.size());
+  for (size_t q = 0; q < images.size(); q++) {           // outputs of k_expand_texels: reserved behind everything that is copied
+    const srt_texture& t = d->textures[images[q].first];
+    texel_item[q] = arena.reserve(nullptr, (size_t)t.width * t.height * sizeof(uchar4), nullptr);
+  }
+  SCK(arena.alloc(s));
+  for (int i = 0; i < d->n_tex; i++)
+    if (tex_image[i] >= 0) texs[i].texels = reinterpret_cast<const uchar4*>(arena.ptr(texel_item[tex_image[i]]));
+  SCK(arena.upload(s));
 #undef SCK
+  for (size_t q = 0; q < images.size(); q++) {
+    const srt_texture& t = d->textures[images[q].first];
+    const size_t px = (size_t)t.width * t.height;
+    k_expand_texels<<<(unsigned)((px + 255) / 256), 256, 0, dev->stream>>>(reinterpret_cast<const unsigned char*>(arena.ptr(images[q].second)),
+                                                                          (size_t)t.width * t.height * t.bpp, t.width, t.height, t.bpp,
+                                                                          reinterpret_cast<uchar4*>(arena.ptr(texel_item[q])));
+  }
 
   // set-up kernels behind the copy, one synchronisation for the whole scene
   if (d->n_tri > 0) k_setup_tris<<<(unsigned)((d->n_tri + 255) / 256), 256, 0, dev->stream>>>(const_cast<Tri*>(s->sc.tris), (int)d->n_tri);

@@ -68,7 +68,7 @@ struct Tex {
   int w, h;                 // IMAGE
   int missing;              // IMAGE: file was missing -> (1,0,1)
   int pad;
-  cudaTextureObject_t obj;  // IMAGE: uchar4 array, point sampled, unnormalised coordinates
+  const uchar4* texels;     // IMAGE: w*h texels in the scene arena, row j at texels + j*w (expanded on the device by k_expand_texels)
 };
 
 #define MAT_NEEDS_UV  1

@@ -221,6 +221,7 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 #define SRT_X2_DEFAULT_TH 8       /* lanes that must still be walking for the walk loop to go on (B200 sweep: 8 < 12 < 16 < 24) */
 #endif
 #define SRT_X2_PARK 160           /* entries per warp: X2_SPH_PARK + 96 */
+#define SRT_X2_PARK_MIN 144       /* X2_SPH_PARK + 80: see fetch_cap in k_wf_extend2 */
 
 // Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint2 entries per warp:
 //   [0, 64)          rays waiting on a leaf that holds a sphere      (slot, leaf node), count ps
@@ -230,7 +231,7 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 // phase (the 4 spheres of configs 3/4 are tested 1.75 times per segment - their boxes span the scene) runs triangle code
 // only for leaves that mix both.  (th_walk bit 8 set: ONE list for both kinds - A/B runs.)
 // Bound on parked rays: fresh rays are fetched only when no ready entry is left, after both lists were cut below 32, so a
-// warp holds at most 32 + 31 + 31 = 94 rays; ps <= 63, pt + r <= 94  ->  park = 64 + 96.
+// warp holds at most 32 + 31 + 31 = 94 rays; ps <= 63, pt + r <= 94  ->  park = 64 + 96 (or less with `fetch_cap`, below).
 // pool.hit[slot] = (prim, t) of the ray's last accepted leaf: (-1, inf) when the ray is fetched, rewritten by every accept;
 // tCur of a parked ray is read back from there.
 template <bool COUNT, int FMT, int THREADS>
@@ -262,6 +263,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
   float tCur = INF;
   int pt = 0, ps = 0, r = 0;        // warp-uniform list counts
   bool pool_dry = false;            // warp-uniform: the wave's rays are all handed out
+  // Fresh rays are fetched only while pt + ps <= fetch_cap: a warp then holds at most 32 + fetch_cap rays, which is what the
+  // shared tri / ready region (park - 64 entries) can take.  park = 160 never restricts (62 <= 64); park = 144 (the lists that
+  // keep config 4's 129 KB tree inside the 164 KB shared-memory configuration, i.e. 64 KB of L1) caps a warp at 80 rays.
+  const int fetch_cap = park - X2_SPH_PARK - 32;
 
   for (;;) {
     // ---- A. lanes whose walk ended are free (their hit is in pool.hit already); lanes stopped on a leaf park their ray
@@ -282,8 +287,9 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     // The end of a wave (no ray left to fetch, none ready): a phase for every idle lane would test one or two leaves at a
     // time, each behind three dependent global loads (64 such phases per warp measured: 10 % of the launch).  Instead the
     // walkers run on until every lane has stopped, and one phase per list serves them all.
+    const bool may_fetch = !pool_dry && pt + ps <= fetch_cap;
     {
-      const bool idle = pool_dry && r == 0 && __ballot_sync(FULL, slot < 0) == FULL;
+      const bool idle = !may_fetch && r == 0 && __ballot_sync(FULL, slot < 0) == FULL;
       if (pt >= 32 || (pt > 0 && idle)) {
         if (two_lists) x2_leaf_phase<COUNT, false>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
         else x2_leaf_phase<COUNT, true>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
@@ -296,7 +302,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     if (m_empty) {
       const int n_empty = __popc(m_empty), q = __popc(m_empty & below);
       const int take = r < n_empty ? r : n_empty;
-      const int fresh = pool_dry ? 0 : n_empty - take;
+      const int fresh = may_fetch ? n_empty - take : 0;
       unsigned long long base = 0;
       if (fresh) {
         const int leader = __ffs(m_empty) - 1;
@@ -342,7 +348,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
       if (pt == 0 && ps == 0 && r == 0 && pool_dry) break;
       continue;
     }
-    const int th = (pool_dry && r == 0) ? 1 : (__popc(mW) < th_walk ? __popc(mW) : th_walk);   // draining: walk until all have stopped
+    const int th = (!may_fetch && r == 0) ? 1 : (__popc(mW) < th_walk ? __popc(mW) : th_walk);   // nothing to refill with: walk until all have stopped
     do {
 #pragma unroll
       for (int rep = 0; rep < SRT_X2_REPS; rep++)

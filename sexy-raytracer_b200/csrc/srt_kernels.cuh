@@ -19,6 +19,18 @@ __global__ void k_setup_tris(Tri* tris, int n) {
   tris[i].a.w = N.x; tris[i].b.w = N.y; tris[i].c.w = N.z; tris[i].d.x = dd;
 }
 
+// image texels: texel (i, j) = (px[0], px[1], px[2], 255) for px = data + j*bpp*w + i*bpp, bytes past the end of the image
+// read 0 (a 1- or 2-byte-per-texel map read with the 3-byte lookup of texture.h:129-148 sees its neighbours)
+__global__ void k_expand_texels(const unsigned char* __restrict__ data, size_t n, int w, int h, int bpp, uchar4* __restrict__ out) {
+  const size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (k >= (size_t)w * (size_t)h) return;
+  const size_t j = k / (size_t)w, i = k % (size_t)w;
+  const size_t off = j * ((size_t)bpp * (size_t)w) + i * (size_t)bpp;
+  uchar4 p;
+  p.x = off < n ? data[off] : 0; p.y = off + 1 < n ? data[off + 1] : 0; p.z = off + 2 < n ? data[off + 2] : 0; p.w = 255;
+  out[k] = p;
+}
+
 // leaf-ordered copies of the primitives for the compact tree (srt_core.cuh: LPrim); runs after k_setup_tris
 __global__ void k_build_lprims(Scene sc, const int32_t* __restrict__ src, int n, LPrim* __restrict__ out) {
   int u = blockIdx.x * blockDim.x + threadIdx.x;

@@ -118,7 +118,7 @@ __device__ __forceinline__ void finish_hit(const Scene& sc, int prim, const Ray&
 
 // ---- texture::value -----------------------------------------------------------------------------
 // imagePNG::value / image3bpp::value (texture.h:129-148, :82-101): the reference's own index
-// arithmetic, then one point-sampled texel fetch through a CUDA texture object.  The uploaded texel
+// arithmetic, then one 4-byte texel load (read-only path).  The expanded texel
 // (i, j) holds (px[0], px[1], px[2]) for px = data + j*bpp*w + i*bpp, which reproduces the
 // "channel 1 of a 1-byte map is the next texel" behaviour of material.h:197.
 __device__ __forceinline__ V3 image_value(const Tex& t, float u, float v) {
@@ -129,7 +129,7 @@ __device__ __forceinline__ V3 image_value(const Tex& t, float u, float v) {
   int j = (int)(v * t.h);
   if (i >= t.w) i = t.w - 1;
   if (j >= t.h) j = t.h - 1;
-  uchar4 px = tex2D<uchar4>(t.obj, (float)i + 0.5f, (float)j + 0.5f);
+  const uchar4 px = __ldg(t.texels + (size_t)j * (size_t)t.w + (size_t)i);     // 0 <= i < w, 0 <= j < h by the lines above
   return mk((float)px.x, (float)px.y, (float)px.z);
 }
 

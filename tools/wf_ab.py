@@ -1,4 +1,4 @@
-"""A/B timing of the wavefront's launch shapes on one GPU: python tools/wf_ab.py <spp> <x2>:<threads>:<th_walk>[:<fused>[:<shade threads>]] [...]
+"""A/B timing of the wavefront's launch shapes on one GPU: python tools/wf_ab.py <spp> <x2>:<threads>:<th_walk>[:<fused>[:<shade threads>[:<shade kernel 1|2|3>[:<park 144|160>]]]] [...]
 (x2 = 0 / 16 / 32 selects k_wf_extend / k_wf_extend2 with 16- / 32-byte nodes; fused = 1: k_wf_path, one launch per frame).
 Config-4 geometry (1280x720, depth 4)."""
 import os, sys
@@ -19,6 +19,9 @@ for cfg in sys.argv[2:]:
     x2, th, walk = f[:3]
     os.environ["SRT_WF_FUSED"] = f[3] if len(f) > 3 else "0"
     os.environ["SRT_WF_SHADE_THREADS"] = f[4] if len(f) > 4 else "256"
+    os.environ["SRT_WF_SHADE"] = f[5] if len(f) > 5 else "2"
+    if len(f) > 6: os.environ["SRT_WF_PARK"] = f[6]
+    else: os.environ.pop("SRT_WF_PARK", None)
     os.environ["SRT_WF_X2"] = x2
     os.environ["SRT_WF"] = "8388608,%s,%s" % (th, walk)
     ds.render(P, want_sum=False, want_rgba=False)
