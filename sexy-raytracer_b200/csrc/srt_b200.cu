@@ -52,7 +52,6 @@ struct srt_device {
   float* d_frame_sum = nullptr; uchar4* d_frame_rgba = nullptr; size_t frame_cap = 0;   // srt_render's device buffers (pixels)
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
-  void* d_wf_ids = nullptr; size_t wf_ids_cap = 0;   // k_wf_shade3: path ids held per shade warp between waves
   void* d_path = nullptr; size_t path_capacity = 0;  // k_wf_path's warp-private path slots (srt_path.cuh)
   void* h_stage = nullptr; size_t h_stage_cap = 0;  // pinned staging of srt_scene_create's arena (scenes up to SCENE_STAGE_MAX bytes)
 };
@@ -119,7 +118,6 @@ void srt_device_destroy(srt_device* d) {
   if (d->wf.ray_o) cudaFree(d->wf.ray_o);
   if (d->d_wf_cur) cudaFree(d->d_wf_cur);
   if (d->d_path) cudaFree(d->d_path);
-  if (d->d_wf_ids) cudaFree(d->d_wf_ids);
   if (d->h_wf_ring) cudaFreeHost(d->h_wf_ring);
   if (d->h_stage) cudaFreeHost(d->h_stage);
   for (int k = 0; k < WF_RING; k++) if (d->wf_ev[k]) cudaEventDestroy(d->wf_ev[k]);

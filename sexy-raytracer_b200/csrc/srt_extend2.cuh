@@ -128,6 +128,9 @@ __device__ __forceinline__ void walk2_step(uint32_t nodes_s, uint32_t hi_off, co
   }
 }
 
+#ifndef SRT_X2_NB
+#define SRT_X2_NB 1     /* leaf tests without early returns (A/B builds: 0 = the early-return forms of srt_core.cuh) */
+#endif
 // aabb::hit / triangle::hit as in srt_core.cuh (same operations, same order, same NaN behaviour) without the early returns:
 // in a leaf phase some lane nearly always needs the last stage, so the returns only cost branches.
 __device__ __forceinline__ bool box_hit_exact_nb(const float4& lo, const float4& hi, const Ray& r, float tMin, float tMax) {
@@ -165,7 +168,11 @@ __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r,
   float4 lo, hi;
   load_node_soa<false>(sc.nodes, 0u, 0u, node, lo, hi);
   if (COUNT) ++cnt.exact;
+#if SRT_X2_NB
   if (!box_hit_exact_nb(lo, hi, r, 0.001f, tCur)) return;
+#else
+  if (!box_hit_exact(lo, hi, r, 0.001f, tCur)) return;
+#endif
   const int pa = __float_as_int(hi.z), pb = __float_as_int(hi.w);
 #pragma unroll 1
   for (int k = 0; k < 2; k++) {
@@ -174,8 +181,13 @@ __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r,
     if (COUNT) { ++cnt.leaves; if (p >= sc.n_tri) ++cnt.sph_leaves; }
     float t;
     bool acc;
+#if SRT_X2_NB
     if (SPH) acc = p < sc.n_tri ? tri_hit_nb(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
     else acc = tri_hit_nb(sc.tris, p, r, 0.001f, t);
+#else
+    if (SPH) acc = p < sc.n_tri ? tri_hit(sc.tris, p, r, 0.001f, t) : sph_hit(sc.sphs, p - sc.n_tri, r, 0.001f, tCur, t);
+    else acc = tri_hit(sc.tris, p, r, 0.001f, t);
+#endif
     if (acc) { tCur = t; prim = p; }
   }
 }

@@ -41,7 +41,7 @@ static const char* tune_env(const char* name) {
 
 struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
-  int wf_slots, wf_th_walk, wf_shade_chunk, wf_shade_threads, wf_shade_kind; const void* wf_shade;     // variant 2
+  int wf_slots, wf_th_walk, wf_shade_chunk, wf_shade_threads; const void* wf_shade;     // variant 2
   int x2_fmt, x2_park;                                                // variant 2 with k_wf_extend2: node bytes (0 = k_wf_extend), entries per warp
   int fused, path_chunk;                                              // variant 2 as ONE launch of k_wf_path (srt_path.cuh); path ids per atomic
 };
@@ -52,9 +52,6 @@ path_fn pick_path(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_path<true, 16, THREADS> : k_wf_path<true, 32, THREADS>;
   return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
 }
-#ifndef SRT_SHADE_DEFAULT
-#define SRT_SHADE_DEFAULT 2
-#endif
 #ifndef SRT_SHADE2_THREADS
 #define SRT_SHADE2_THREADS 256
 #endif
@@ -133,17 +130,10 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
       if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
       size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
       if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
-      // The SM splits 256 KB between shared memory and L1 in steps (.., 100, 132, 164, 196, 228 KB + 1 KB reserved per CTA), and
-      // the leaf phases live on what is left for L1 (config 4: 1.385 ms per launch with 92 KB, 1.51 ms with 28 KB).  If shorter
-      // park lists (144 entries: a warp then holds at most 80 rays instead of 94) reach the next step down, take them.
+      // (SRT_WF_PARK=144: shorter lists that keep config 4's tree inside the 164 KB shared-memory step, i.e. 92 KB of L1 instead
+      // of 60 - measured: L1 hit rate 26 -> 37 %, but a warp capped at 80 rays runs more partial phases: 1.483 vs 1.454 ms)
       plan.x2_park = SRT_X2_PARK;
-      {
-        static const size_t steps[] = {8, 16, 32, 64, 100, 132, 164, 196, 228};
-        auto step_of = [&](size_t dyn) { const size_t b = dyn + fa2.sharedSizeBytes + 1024; for (size_t k : steps) if (b <= k * 1024) return k; return (size_t)256; };
-        const size_t need_min = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK_MIN);
-        if (step_of(need_min) < step_of(need)) { plan.x2_park = SRT_X2_PARK_MIN; need = need_min; }
-        if (const char* e = tune_env("SRT_WF_PARK")) { const int k = atoi(e); if (k == SRT_X2_PARK || k == SRT_X2_PARK_MIN) { plan.x2_park = k; need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, k); } }
-      }
+      if (const char* e = tune_env("SRT_WF_PARK")) { const int k = atoi(e); if (k == SRT_X2_PARK || k == SRT_X2_PARK_MIN) { plan.x2_park = k; need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, k); } }
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
       if (!wf_env) plan.wf_th_walk = SRT_X2_DEFAULT_TH;
       break;
@@ -170,16 +160,14 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
                                          : pick_extend<512>(dev->counters, mode);
     plan.fn = (const void*)fn;
   }
-  {   // SRT_WF_SHADE=1: one thread per slot; 2: sorted passes over 512-slot chunks per block; 3: the same per warp, no barriers
-    int kind = SRT_SHADE_DEFAULT;
-    if (const char* sh = tune_env("SRT_WF_SHADE")) { const int v = atoi(sh); if (v >= 1 && v <= 3) kind = v; }
+  {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
+    const char* sh = tune_env("SRT_WF_SHADE");
+    const bool sorted = !(sh && atoi(sh) == 1);
     int ts = SRT_SHADE2_THREADS;
     if (const char* t = tune_env("SRT_WF_SHADE_THREADS")) ts = atoi(t) == 128 ? 128 : 256;
-    plan.wf_shade_kind = kind;
-    plan.wf_shade_threads = kind == 2 ? ts : 256;
-    plan.wf_shade_chunk = kind == 2 ? 2 * ts : kind == 3 ? 512 : 256;      // slots per block and round
-    if (kind == 1) plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
-    else if (kind == 3) plan.wf_shade = dev->counters ? (const void*)k_wf_shade3<true> : (const void*)k_wf_shade3<false>;
+    plan.wf_shade_threads = sorted ? ts : 256;
+    plan.wf_shade_chunk = sorted ? 2 * ts : 256;
+    if (!sorted) plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
     else if (ts == 128) plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 128> : (const void*)k_wf_shade2<false, 128>;
     else plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 256> : (const void*)k_wf_shade2<false, 256>;
   }
@@ -323,10 +311,7 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   const unsigned long long total = (unsigned long long)plan.A.n_tiles * 32ull * (unsigned long long)plan.A.sample_count;
   Scene sc = s->sc; RenderArgs A = plan.A; WfCursors* cur = dev->d_wf_cur; unsigned long long* ctr = dev->d_counters;
   int th_walk = plan.wf_th_walk;
-  // k_wf_shade3: the path ids every shade warp holds between waves (zeroed per frame), ids per draw
-  ulonglong2* warp_ids = nullptr;
-  int chunk_ids = 1024;
-  void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr, &warp_ids, &chunk_ids};     // (the last two: k_wf_shade3 only)
+  void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
   int x2_park = plan.x2_park;
   void* extend_args_v1[] = {&sc, &pool, &cur, &th_walk, &ctr};
   void* extend_args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
@@ -338,18 +323,6 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
     if (shade_blocks > chunks) shade_blocks = chunks;
   }
   int launches = 0;
-  if (plan.wf_shade_kind == 3) {
-    const size_t nw = (size_t)shade_blocks * 8;
-    if (dev->wf_ids_cap < nw) {
-      if (dev->d_wf_ids) { CK(cudaFree(dev->d_wf_ids)); dev->d_wf_ids = nullptr; dev->wf_ids_cap = 0; }
-      CK(cudaMalloc(&dev->d_wf_ids, nw * sizeof(ulonglong2)));
-      dev->wf_ids_cap = nw;
-    }
-    warp_ids = (ulonglong2*)dev->d_wf_ids;
-    CK(cudaMemsetAsync(warp_ids, 0, nw * sizeof(ulonglong2), dev->stream));
-    const unsigned long long per_draw = total / ((unsigned long long)nw * 4) / 32 * 32;
-    chunk_ids = (int)std::min<unsigned long long>(1024, std::max<unsigned long long>(32, per_draw));
-  }
 
   CK(cudaMemsetAsync(dev->d_counters, 0, 8 * sizeof(unsigned long long), dev->stream));
   CK(cudaMemsetAsync(cur, 0, sizeof(WfCursors), dev->stream));

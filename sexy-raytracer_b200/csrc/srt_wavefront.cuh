@@ -384,6 +384,10 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
 //   pass 1  (thread = list item) : shade_segment for the listed hits; paths that end retire
 //   pass 2  (thread = list item) : retired / empty slots take the next path ids of the frame and generate their ray
 // Same arithmetic, same Philox keys; only which thread serves which slot and the order paths are numbered change.
+// The block barriers between the passes are what keeps this kernel fast: a barrier-free version (one warp per 64 slots,
+// path ids drawn 1024 at a time per warp) ran 2.4x slower - with the warps of an SM spread over 4.7 k instructions of
+// shading code the instruction cache misses all the time (ncu: 20 warps stalled on no_instruction per issue against 2.5
+// here, profiles/r2_extend2_ab.md).  The same effect sank the fused kernel (srt_path.cuh).
 template <bool COUNT, int TS>
 __global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shade2(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
                                                    unsigned long long* counters) {
@@ -520,162 +524,6 @@ __global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shad
   if (threadIdx.x == 0) {
     if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
     if (s_stat[1]) { atomicAdd(&counters[1], s_stat[1]); cur->alive = 1; }
-    if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
-  }
-}
-
-// ---- SHADE + REGENERATE without block barriers ----------------------------------------------------------------------
-// k_wf_shade2 spends a quarter of its stall samples at its __syncthreads() (ncu, profiles/r2_extend2_ab.md): the eight warps
-// of a block wait for the one that drew the expensive materials.  Here a WARP owns 64 slots at a time - lists of 64 bytes in
-// shared memory, compacted with warp votes, __syncwarp() only - so a warp that is done takes its next 64 slots at once.
-// What made per-warp regeneration unusable before was one global atomic per warp and chunk on the single path cursor
-// (r1_wavefront.md); a warp now draws `chunk_ids` path ids at a time (1024 = 32 pixel tiles of one sample index) and keeps
-// what it has not used in `warp_ids` for the next wave.  Same arithmetic, same Philox keys as the other shade kernels.
-template <bool COUNT>
-__global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade3(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
-                                                   unsigned long long* counters, ulonglong2* __restrict__ warp_ids, int chunk_ids) {
-  __shared__ unsigned char s_list[8][2][64];
-  __shared__ unsigned long long s_stat[3];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1;
-  if (blockIdx.x == 0 && threadIdx.x == 0) cur->ray = 0;    // the next extend wave starts at slot 0
-  if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
-  __syncthreads();                                          // (the only block barrier before the statistics)
-  const unsigned long long per_sample = (unsigned long long)A.n_tiles * 32ull;
-  const unsigned long long total = per_sample * (unsigned long long)A.sample_count;
-  const long long gw = (long long)blockIdx.x * 8 + warp, n_gw = (long long)gridDim.x * 8;
-  ulonglong2 ids = warp_ids[gw];                            // [x, y): path ids this warp still holds
-  bool exhausted = false;                                   // the frame's cursor has run past `total`
-  unsigned char* s_hit = s_list[warp][0];
-  unsigned char* s_free = s_list[warp][1];
-  Counters cnt = {0, 0, 0, 0, 0};
-  unsigned n_new = 0, n_seg = 0;
-
-  for (long long c = gw; c * 64 < (long long)pool.n_slots; c += n_gw) {
-    const long long base = c * 64;
-    {   // this warp's next 64 slots: 3 x 8 + 2 x 4 lines of 128 bytes, one per lane, towards the L2
-      const long long nb = (c + n_gw) * 64;
-      if (nb + 64 <= (long long)pool.n_slots) {
-        const void* p = lane < 24 ? (const void*)((lane < 8 ? pool.thr : lane < 16 ? pool.ray_o : pool.ray_d) + nb + (lane & 7) * 8)
-                                  : (const void*)(lane < 28 ? (const void*)(pool.hit + nb + (lane & 3) * 16) : (const void*)(pool.id + nb + (lane & 3) * 16));
-        asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-      }
-    }
-    // ---- pass 0: classify two slots per lane (all loads first)
-    float4 t4[2]; int2 h[2]; uint32_t pix[2];
-#pragma unroll
-    for (int q = 0; q < 2; q++) {
-      const long long k = base + q * 32 + lane;
-      t4[q] = make_float4(0, 0, 0, __int_as_float(-2)); h[q] = make_int2(-1, 0); pix[q] = 0;
-      if (k < (long long)pool.n_slots) { t4[q] = pool.thr[k]; h[q] = pool.hit[k]; pix[q] = pool.id[k].x; }
-    }
-    int n_hit = 0, n_free = 0;
-#pragma unroll
-    for (int q = 0; q < 2; q++) {
-      const int bounce = __float_as_int(t4[q].w);
-      bool is_hit = false, is_free = false;
-      if (bounce == -1) is_free = true;                                    // no path in this slot (-2: beyond the pool)
-      else if (bounce >= 0) {
-        if (h[q].x < 0) {                                                  // miss -> background, main.cpp:39-40
-          float* px = accum + (size_t)pix[q] * 3;
-          atomicAdd(px, t4[q].x * A.bg[0]); atomicAdd(px + 1, t4[q].y * A.bg[1]); atomicAdd(px + 2, t4[q].z * A.bg[2]);
-          is_free = true;
-        } else is_hit = true;
-      }
-      const unsigned mh = __ballot_sync(FULL, is_hit), mf = __ballot_sync(FULL, is_free);
-      if (is_hit) s_hit[n_hit + __popc(mh & below)] = (unsigned char)(q * 32 + lane);
-      if (is_free) s_free[n_free + __popc(mf & below)] = (unsigned char)(q * 32 + lane);
-      n_hit += __popc(mh); n_free += __popc(mf);
-    }
-    __syncwarp();
-    // ---- pass 1: shade the hits; paths that end join the free list
-    for (int t0 = 0; t0 < n_hit; t0 += 32) {
-      const int t = t0 + lane;
-      bool done = false;
-      int j = 0;
-      if (t < n_hit) {
-        j = s_hit[t];
-        const long long k = base + j;
-        const float4 th4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k];
-        const int2 hh = pool.hit[k];
-        const uint2 id = pool.id[k];
-        int bounce = __float_as_int(th4.w);
-        Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
-        V3 thr = mk(th4.x, th4.y, th4.z), L = mk(0, 0, 0);
-        done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
-        if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                    // this segment's emitted term (NaN included)
-          float* px = accum + (size_t)id.x * 3;
-          atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
-        }
-        if (!done) {
-          pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-          pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
-          pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
-          ++n_seg;
-        }
-      }
-      const unsigned md = __ballot_sync(FULL, done);
-      if (done) s_free[n_free + __popc(md & below)] = (unsigned char)j;
-      n_free += __popc(md);
-    }
-    __syncwarp();
-    // ---- pass 2: regenerate from the warp's own run of path ids
-    for (int t0 = 0; t0 < n_free; t0 += 32) {
-      const int want = n_free - t0 < 32 ? n_free - t0 : 32;
-      long long myid = -1;
-      int served = 0;
-      while (served < want) {
-        if (ids.x >= ids.y) {
-          if (exhausted) break;
-          unsigned long long b = 0;
-          if (lane == 0) b = atomicAdd(&cur->path, (unsigned long long)chunk_ids);
-          b = __shfl_sync(FULL, b, 0);
-          if (b >= total) { exhausted = true; break; }
-          ids.x = b; ids.y = b + (unsigned long long)chunk_ids < total ? b + (unsigned long long)chunk_ids : total;
-        }
-        const unsigned long long left = ids.y - ids.x;
-        const int avail = left < (unsigned long long)(want - served) ? (int)left : want - served;
-        if (lane >= served && lane < served + avail) myid = (long long)(ids.x + (unsigned long long)(lane - served));
-        ids.x += (unsigned long long)avail; served += avail;
-      }
-      if (lane < want) {
-        const long long k = base + s_free[t0 + lane];
-        bool made = false;
-        if (myid >= 0) {
-          const unsigned q = (unsigned)((unsigned long long)myid % per_sample);
-          const int s_off = (int)((unsigned long long)myid / per_sample);
-          const int tile = (int)(q >> 5), l = (int)(q & 31);
-          const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
-          if (x < A.W && y < A.H) {
-            const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
-            const Ray r = generate_ray(A, x, y, pixel, sample);
-            pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-            pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
-            pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
-            pool.id[k] = make_uint2(pixel, sample);
-            made = true; ++n_new; ++n_seg;
-          }
-        }
-        if (!made) {                                  // no path: extend skips the slot, the next shade pass retries
-          pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
-          pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
-        }
-      }
-    }
-    __syncwarp();                                     // the lists are reused by the warp's next 64 slots
-  }
-  if (lane == 0) warp_ids[gw] = ids;
-  const bool holds_ids = ids.x < ids.y;               // unused path ids: the frame is not over even if nothing was traced
-  unsigned long long v0 = n_new, v1 = n_seg, v2 = cnt.tri_hits;
-  for (int o = 16; o > 0; o >>= 1) {
-    v0 += __shfl_down_sync(FULL, v0, o); v1 += __shfl_down_sync(FULL, v1, o);
-    if (COUNT) v2 += __shfl_down_sync(FULL, v2, o);
-  }
-  if (lane == 0) { atomicAdd(&s_stat[0], v0); atomicAdd(&s_stat[1], v1 + (holds_ids ? (1ull << 40) : 0ull)); if (COUNT) atomicAdd(&s_stat[2], v2); }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
-    if (s_stat[1]) { if (s_stat[1] & ((1ull << 40) - 1)) atomicAdd(&counters[1], s_stat[1] & ((1ull << 40) - 1)); cur->alive = 1; }
     if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
   }
 }
