@@ -42,7 +42,7 @@ namespace srt {
    >= 0: walking (FMT 32: byte offset of the node, FMT 16: node index) */
 #define X2_KIND_SHIFT(FMT) ((FMT) == 32 ? 24 : 14)
 #define X2_MAX_NODES(FMT) ((FMT) == 32 ? (1 << 24) - 1 : 16382)   /* FMT 16: -2 - (16382 | 1 << 14) = -32768 still fits 16 bits */
-#define X2_SPH_PARK 64               /* entries of a warp's sphere-leaf list (it never holds more than 63)  */
+#define X2_SPH_PARK 64               /* k_wf_path: entries of a warp's sphere-leaf list (it never holds more than 63)  */
 
 struct Aux2 { float idx, idy, idz, oidx, oidy, oidz, nMs; };
 
@@ -192,29 +192,25 @@ __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r,
   }
 }
 
-// One leaf phase of a warp: the top `take` <= 32 entries of `list` (count `n_list`), one per lane.  An entry is 8 bytes
-// (slot, leaf node): the ray comes from the pool, tCur from pool.hit[slot].y - (prim, t) of the last accept live THERE, written
-// when a leaf accepts, so a parked ray costs 8 bytes of shared memory instead of 16 (the L1 that is left decides how fast the
-// phases' loads come back: 228 KB minus the shared memory in use).  Rays whose walk goes on are pushed on the ready stack
-// (ready_top[-1 - k] = (slot, next state)); a ray whose leaf was the last node is simply done - its hit is already stored.
-template <bool COUNT, bool SPH>
-__device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& pool, uint2* list, int& n_list, uint2* ready_top, int& r,
+// One leaf phase of a warp: the top `take` <= 32 entries of the pending list, one per lane; rays whose walk goes on are
+// pushed on the ready stack (ready_top[-1 - k]); a ray whose leaf was the last node has its hit stored at once.
+template <bool COUNT>
+__device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& pool, uint4* list, int& n_list, uint4* ready_top, int& r,
                                               int lane, int n, int step_scale, Counters& cnt) {
   const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1u;
   const int take = n_list < 32 ? n_list : 32;
   bool push = false;
-  uint2 res = make_uint2(0, 0);
+  uint4 res = make_uint4(0, 0, 0, 0);
   if (lane < take) {
-    const uint2 q = list[n_list - take + lane];
+    const uint4 q = list[n_list - take + lane];
     const float4 d = __ldg(&pool.ray_d[q.x]), o = __ldg(&pool.ray_o[q.x]);
-    const int2 h = pool.hit[q.x];                                             // (written by this kernel: no __ldg)
     Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
-    float tc = __int_as_float(h.y);
-    int pr = -1;
-    x2_leaf<COUNT, SPH>(sc, (int)q.y, ry, tc, pr, cnt);
-    if (pr >= 0) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));           // an accept
+    float tc = __uint_as_float(q.z);
+    int pr = (int)q.w;
+    x2_leaf<COUNT, true>(sc, (int)q.y, ry, tc, pr, cnt);
     const int nxt = (int)q.y + 1;
-    if (nxt < n) { push = true; res = make_uint2(q.x, (unsigned)(nxt * step_scale)); }
+    if (nxt >= n) pool.hit[q.x] = make_int2(pr, __float_as_int(tc));          // the leaf was the last node: the walk is over
+    else { push = true; res = make_uint4(q.x, (unsigned)(nxt * step_scale), __float_as_uint(tc), (unsigned)pr); }
   }
   n_list -= take;
   const unsigned mp = __ballot_sync(FULL, push);      // (also orders the reads above before the writes below)
@@ -224,7 +220,7 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 }
 
 #ifndef SRT_X2_REPS
-#define SRT_X2_REPS 4             /* box tests per vote: 4 measured 3.6 % ahead of 2 (B200, config 4) */
+#define SRT_X2_REPS 2             /* box tests per vote (B200, config 4, th_walk 8: 2 -> 1.385 ms per launch, 4 -> 1.403) */
 #endif
 #ifndef SRT_X2_DEFAULT_FMT
 #define SRT_X2_DEFAULT_FMT 32     /* node bytes plan_render asks for first: 16, 32, or 0 = keep k_wf_extend */
@@ -232,33 +228,29 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 #ifndef SRT_X2_DEFAULT_TH
 #define SRT_X2_DEFAULT_TH 8       /* lanes that must still be walking for the walk loop to go on (B200 sweep: 8 < 12 < 16 < 24) */
 #endif
-#define SRT_X2_PARK 160           /* entries per warp: X2_SPH_PARK + 96 */
-#define SRT_X2_PARK_MIN 144       /* X2_SPH_PARK + 80: see fetch_cap in k_wf_extend2 */
+#define SRT_X2_PARK 64            /* park entries per warp */
+#ifndef SRT_X2_PREFETCH
+#define SRT_X2_PREFETCH 0
+#endif
 
-// Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint2 entries per warp:
-//   [0, 64)          rays waiting on a leaf that holds a sphere      (slot, leaf node), count ps
-//   [64, 64 + pt)    rays waiting on a leaf of triangles only        (same), count pt
-//   [park - r, park) rays whose leaf is done and whose walk goes on  (slot, next state)
-// Two pending lists, because a phase costs what its slowest lane costs: a triangle phase runs no sphere code, a sphere
-// phase (the 4 spheres of configs 3/4 are tested 1.75 times per segment - their boxes span the scene) runs triangle code
-// only for leaves that mix both.  (th_walk bit 8 set: ONE list for both kinds - A/B runs.)
-// Bound on parked rays: fresh rays are fetched only when no ready entry is left, after both lists were cut below 32, so a
-// warp holds at most 32 + 31 + 31 = 94 rays; ps <= 63, pt + r <= 94  ->  park = 64 + 96 (or less with `fetch_cap`, below).
-// pool.hit[slot] = (prim, t) of the ray's last accepted leaf: (-1, inf) when the ray is fetched, rewritten by every accept;
-// tCur of a parked ray is read back from there.
+// Shared memory: the staged nodes (FMT 32: lo[n] | hi[n], FMT 16: q[n]) followed by `park` uint4 entries per warp:
+// pending entries (slot, leaf node, tCur, prim) grow from index 0, ready entries (slot, next state, tCur, prim) from the top.
+// A warp never holds more than 63 parked rays (fresh rays are fetched only when no ready one is left and fewer than 32 are
+// pending), so park = 64 always suffices: 32 KB per CTA, which keeps config 4's 129 KB tree inside the 164 KB shared-memory
+// step of the SM - i.e. leaves 64 KB of L1 for the rays and primitives the leaf phases re-read.  Measured alternatives
+// (profiles/r2_extend2_ab.md): separate lists for leaves with / without a sphere make the phases 1.4 % cheaper but need 160
+// entries per warp: with 16-byte entries (209 KB, 19 KB of L1) 1.50 ms per launch against 1.385; with 8-byte entries and the
+// ray's (prim, tCur) kept in pool.hit (170 KB, the 196 KB step) 1.43-1.45.
 template <bool COUNT, int FMT, int THREADS>
-__global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk_arg, int park,
+__global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
                                                           unsigned long long* counters) {
   extern __shared__ uint4 smem_x2[];
   const int n = sc.n_nodes;
-  const bool two_lists = (th_walk_arg & 0x100) == 0;
-  const int th_walk = th_walk_arg & 0xff;
-  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, two_lists);
+  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, false);
   const int node_u4 = FMT == 32 ? 2 * n : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint2* s_sph = reinterpret_cast<uint2*>(smem_x2 + node_u4) + warp * park;
-  uint2* s_tri = s_sph + X2_SPH_PARK;
-  uint2* s_top = s_sph + park;                      // ready entries: s_top[-1 - k]
+  uint4* s_park = smem_x2 + node_u4 + warp * park;
+  uint4* s_top = s_park + park;                     // ready entries: s_top[-1 - k]
   const uint32_t nodes_s = (uint32_t)__cvta_generic_to_shared(smem_x2);
   const uint32_t hi_off = (uint32_t)n * 16u;
   __syncthreads();
@@ -266,55 +258,42 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
   const float INF = __int_as_float(0x7f800000);
   const int root = n > 0 ? 0 : X2_DONE;
   const int step_scale = FMT == 32 ? 16 : 1;
-  constexpr int KSH = X2_KIND_SHIFT(FMT);
   Counters cnt = {0, 0, 0, 0, 0};
   if (blockIdx.x == 0 && threadIdx.x == 0) cur->alive = 0;   // set anew by the next shade pass
 
   Aux2 x = {0, 0, 0, 0, 0, 0, 0};
-  int i = X2_DONE, slot = -1;
+  int i = X2_DONE, slot = -1, prim = -1;
   float tCur = INF;
-  int pt = 0, ps = 0, r = 0;        // warp-uniform list counts
+  int p = 0, r = 0;                 // warp-uniform: pending entries [0, p), ready entries [park - r, park)
   bool pool_dry = false;            // warp-uniform: the wave's rays are all handed out
-  // Fresh rays are fetched only while pt + ps <= fetch_cap: a warp then holds at most 32 + fetch_cap rays, which is what the
-  // shared tri / ready region (park - 64 entries) can take.  park = 160 never restricts (62 <= 64); park = 144 (the lists that
-  // keep config 4's 129 KB tree inside the 164 KB shared-memory configuration, i.e. 64 KB of L1) caps a warp at 80 rays.
-  const int fetch_cap = park - X2_SPH_PARK - 32;
 
   for (;;) {
-    // ---- A. lanes whose walk ended are free (their hit is in pool.hit already); lanes stopped on a leaf park their ray
-    const bool stp = slot >= 0 && i <= -2;
-    const int code = -2 - i;
-    const bool stp_s = stp && (code >> KSH) != 0;
-    const unsigned ms = __ballot_sync(FULL, stp), mss = __ballot_sync(FULL, stp_s);
+    // ---- A. lanes whose walk ended store the hit; lanes stopped on a leaf park their ray
+    const bool has = slot >= 0;
+    const bool stp = has && i <= -2;
+    if (has && i == X2_DONE) { pool.hit[slot] = make_int2(prim, __float_as_int(tCur)); slot = -1; }
+    const unsigned ms = __ballot_sync(FULL, stp);
     if (stp) {
-      const uint2 e = make_uint2((unsigned)slot, (unsigned)(code & ((1 << KSH) - 1)));
-      if (stp_s) s_sph[ps + __popc(mss & below)] = e;
-      else s_tri[pt + __popc(ms & ~mss & below)] = e;
+      s_park[p + __popc(ms & below)] = make_uint4((unsigned)slot, (unsigned)(-2 - i), __float_as_uint(tCur), (unsigned)prim);
+#if SRT_X2_PREFETCH
+      asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.nodes + (-2 - i)));      // the leaf's true box + primitive ids, for the phase
+#endif
+      slot = -1; i = X2_DONE;
     }
-    if (i < 0) slot = -1;
-    if (stp) i = X2_DONE;
-    ps += __popc(mss); pt += __popc(ms & ~mss);
+    p += __popc(ms);
     __syncwarp();
-    // ---- B. leaf phases: 32 parked rays of one list, one per lane (fewer only when nothing else can fill the lanes)
+    // ---- B. leaf phase: 32 parked rays, one per lane.
     // The end of a wave (no ray left to fetch, none ready): a phase for every idle lane would test one or two leaves at a
-    // time, each behind three dependent global loads (64 such phases per warp measured: 10 % of the launch).  Instead the
-    // walkers run on until every lane has stopped, and one phase per list serves them all.
-    const bool may_fetch = !pool_dry && pt + ps <= fetch_cap;
-    {
-      const bool idle = !may_fetch && r == 0 && __ballot_sync(FULL, slot < 0) == FULL;
-      if (pt >= 32 || (pt > 0 && idle)) {
-        if (two_lists) x2_leaf_phase<COUNT, false>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
-        else x2_leaf_phase<COUNT, true>(sc, pool, s_tri, pt, s_top, r, lane, n, step_scale, cnt);
-      }
-      if (ps >= 32 || (ps > 0 && idle))
-        x2_leaf_phase<COUNT, true>(sc, pool, s_sph, ps, s_top, r, lane, n, step_scale, cnt);
-    }
+    // time, each behind three dependent global loads (64 such phases per warp measured).  Instead the walkers run on until
+    // every lane has stopped, and one phase serves them all.
+    if (p >= 32 || (p > 0 && pool_dry && r == 0 && __ballot_sync(FULL, slot < 0) == FULL))
+      x2_leaf_phase<COUNT>(sc, pool, s_park, p, s_top, r, lane, n, step_scale, cnt);
     // ---- C. empty lanes take a ready ray, else the next ray of the wave (one atomic per warp)
     const unsigned m_empty = __ballot_sync(FULL, slot < 0);
     if (m_empty) {
       const int n_empty = __popc(m_empty), q = __popc(m_empty & below);
       const int take = r < n_empty ? r : n_empty;
-      const int fresh = may_fetch ? n_empty - take : 0;
+      const int fresh = pool_dry ? 0 : n_empty - take;
       unsigned long long base = 0;
       if (fresh) {
         const int leader = __ffs(m_empty) - 1;
@@ -327,22 +306,18 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
         int link = root;
         bool is_fresh = false;
         if (q < take) {
-          const uint2 e = s_top[-1 - (r - take + q)];
-          mine = (long long)e.x; link = (int)e.y;
+          const uint4 e = s_top[-1 - (r - take + q)];
+          mine = (long long)e.x; link = (int)e.y; tCur = __uint_as_float(e.z); prim = (int)e.w;
         } else if (q - take < fresh) {
           const unsigned long long idx = base + (unsigned long long)(q - take);
-          if (idx < (unsigned long long)pool.n_slots) { mine = (long long)idx; is_fresh = true; }
+          if (idx < (unsigned long long)pool.n_slots) { mine = (long long)idx; tCur = INF; prim = -1; is_fresh = true; }
         }
         if (mine >= 0) {
           const float4 d = __ldg(&pool.ray_d[mine]), o = __ldg(&pool.ray_o[mine]);
-          if (!is_fresh) tCur = __int_as_float(pool.hit[mine].y);
-          else tCur = INF;
           if (!is_fresh || __float_as_int(d.w) == 1) {
             Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
-            if (make_aux2(ry, sc.x2_centre, x)) {
-              slot = (int)mine; i = link;
-              if (is_fresh) pool.hit[mine] = make_int2(-1, __float_as_int(INF));
-            } else {                                 // only a fresh ray can land here: the exact ordered walk, start to end
+            if (make_aux2(ry, sc.x2_centre, x)) { slot = (int)mine; i = link; }
+            else {                                   // only a fresh ray can land here: the exact ordered walk, start to end
               int pr; float t;
               traverse<COUNT>(sc, sc.nodes, ry, 0.001f, INF, pr, t, &cnt);
               pool.hit[mine] = make_int2(pr, __float_as_int(t));
@@ -357,10 +332,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     const unsigned mW = __ballot_sync(FULL, i >= 0);
     if (!mW) {
       if (__ballot_sync(FULL, slot >= 0)) continue;          // finished / stopped lanes only: serve them
-      if (pt == 0 && ps == 0 && r == 0 && pool_dry) break;
+      if (p == 0 && r == 0 && pool_dry) break;
       continue;
     }
-    const int th = (!may_fetch && r == 0) ? 1 : (__popc(mW) < th_walk ? __popc(mW) : th_walk);   // nothing to refill with: walk until all have stopped
+    const int th = (pool_dry && r == 0) ? 1 : (__popc(mW) < th_walk ? __popc(mW) : th_walk);   // nothing to refill with: walk until all have stopped
     do {
 #pragma unroll
       for (int rep = 0; rep < SRT_X2_REPS; rep++)

@@ -65,9 +65,9 @@ extend2_fn pick_extend2(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_extend2<true, 16, THREADS> : k_wf_extend2<true, 32, THREADS>;
   return fmt == 16 ? k_wf_extend2<false, 16, THREADS> : k_wf_extend2<false, 32, THREADS>;
 }
-// shared memory of k_wf_extend2: the staged nodes + `park` 8-byte entries per warp
+// shared memory of k_wf_extend2: the staged nodes + `park` 16-byte entries per warp
 static size_t x2_smem_bytes(int n_nodes, int fmt, int threads, int park) {
-  return (size_t)n_nodes * (size_t)fmt + (size_t)(threads / 32) * (size_t)park * 8;
+  return (size_t)n_nodes * (size_t)fmt + (size_t)(threads / 32) * (size_t)park * 16;
 }
 
 typedef void (*extend_fn)(Scene, WfPool, WfCursors*, int, unsigned long long*);
@@ -128,12 +128,9 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
                        : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
                                              : (const void*)pick_extend2<512>(dev->counters, fmt);
       if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
-      size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
+      const size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
       if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
-      // (SRT_WF_PARK=144: shorter lists that keep config 4's tree inside the 164 KB shared-memory step, i.e. 92 KB of L1 instead
-      // of 60 - measured: L1 hit rate 26 -> 37 %, but a warp capped at 80 rays runs more partial phases: 1.483 vs 1.454 ms)
       plan.x2_park = SRT_X2_PARK;
-      if (const char* e = tune_env("SRT_WF_PARK")) { const int k = atoi(e); if (k == SRT_X2_PARK || k == SRT_X2_PARK_MIN) { plan.x2_park = k; need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, k); } }
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
       if (!wf_env) plan.wf_th_walk = SRT_X2_DEFAULT_TH;
       break;
