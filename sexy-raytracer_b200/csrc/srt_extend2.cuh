@@ -80,7 +80,7 @@ __device__ __forceinline__ unsigned pack_h2(__half a, __half b) { return (unsign
 // One node of the caller's threaded tree (srt_core.cuh: Node) -> the walk's record.  Links: >= 0 next node, X2_DONE, or
 // (-2 - k) = stop on leaf k.
 template <int FMT>
-__device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes, bool two_lists = true) {
+__device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes, bool two_lists = true, int hi_index = -1) {
   const int n = sc.n_nodes;
   const float4 lo = __ldg(&sc.nodes[k].lo), hi = __ldg(&sc.nodes[k].hi);
   const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
@@ -96,7 +96,7 @@ __device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes
   const float hx = x2_hi(lo.w, c[0]), hy = x2_hi(hi.x, c[1]), hz = x2_hi(hi.y, c[2]);
   if (FMT == 32) {
     s_nodes[k] = make_uint4(__float_as_uint(lx), __float_as_uint(ly), __float_as_uint(lz), __float_as_uint(hx));
-    s_nodes[n + k] = make_uint4(__float_as_uint(hy), __float_as_uint(hz), (unsigned)link_miss, (unsigned)link_hit);
+    s_nodes[(hi_index < 0 ? n : hi_index) + k] = make_uint4(__float_as_uint(hy), __float_as_uint(hz), (unsigned)link_miss, (unsigned)link_hit);
   } else {
     s_nodes[k] = make_uint4(pack_h2(__float2half_rd(lx), __float2half_rd(ly)), pack_h2(__float2half_rd(lz), __float2half_ru(hx)),
                             pack_h2(__float2half_ru(hy), __float2half_ru(hz)), ((unsigned)link_miss << 16) | ((unsigned)link_hit & 0xffffu));
@@ -241,18 +241,21 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 // (profiles/r2_extend2_ab.md): separate lists for leaves with / without a sphere make the phases 1.4 % cheaper but need 160
 // entries per warp: with 16-byte entries (209 KB, 19 KB of L1) 1.50 ms per launch against 1.385; with 8-byte entries and the
 // ray's (prim, tCur) kept in pool.hit (170 KB, the 196 KB step) 1.43-1.45.
-template <bool COUNT, int FMT, int THREADS>
+// HIOFF (FMT 32 only): byte offset of the hi[] half of the nodes when it is a compile-time constant (the host picks 65536
+// for trees of 2049-4096 nodes) - the second LDS.128 of a step then takes its address from the same register with an
+// immediate offset instead of an extra add per step; 0 = hi[] follows lo[] at n * 16.
+template <bool COUNT, int FMT, int THREADS, int HIOFF = 0>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
                                                           unsigned long long* counters) {
   extern __shared__ uint4 smem_x2[];
   const int n = sc.n_nodes;
-  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, false);
-  const int node_u4 = FMT == 32 ? 2 * n : n;
+  for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, false, HIOFF ? HIOFF / 16 : -1);
+  const int node_u4 = FMT == 32 ? (HIOFF ? HIOFF / 16 + n : 2 * n) : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint4* s_park = smem_x2 + node_u4 + warp * park;
   uint4* s_top = s_park + park;                     // ready entries: s_top[-1 - k]
   const uint32_t nodes_s = (uint32_t)__cvta_generic_to_shared(smem_x2);
-  const uint32_t hi_off = (uint32_t)n * 16u;
+  const uint32_t hi_off = HIOFF ? (uint32_t)HIOFF : (uint32_t)n * 16u;
   __syncthreads();
   const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1u;
   const float INF = __int_as_float(0x7f800000);

@@ -52,6 +52,12 @@ path_fn pick_path(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_path<true, 16, THREADS> : k_wf_path<true, 32, THREADS>;
   return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
 }
+#ifndef SRT_X2_HIOFF_DEFAULT
+#define SRT_X2_HIOFF_DEFAULT 1
+#endif
+#ifndef SRT_SHADE_DEFAULT
+#define SRT_SHADE_DEFAULT 2
+#endif
 #ifndef SRT_SHADE2_THREADS
 #define SRT_SHADE2_THREADS 256
 #endif
@@ -128,7 +134,14 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
                        : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
                                              : (const void*)pick_extend2<512>(dev->counters, fmt);
       if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
-      const size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
+      size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
+      // 2049-4096 nodes at the default CTA size: hi[] at the constant offset 64 KB (k_wf_extend2's HIOFF), 64 KB - n * 16 bytes more
+      const char* ho = tune_env("SRT_WF_HIOFF");
+      if (fmt == 32 && plan.threads == 1024 && s->sc.n_nodes > 2048 && s->sc.n_nodes <= 4096 && !(ho && atoi(ho) == 0) && SRT_X2_HIOFF_DEFAULT) {
+        f2 = dev->counters ? (const void*)k_wf_extend2<true, 32, 1024, 65536> : (const void*)k_wf_extend2<false, 32, 1024, 65536>;
+        need += 65536 - (size_t)s->sc.n_nodes * 16;
+        if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
+      }
       if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
       plan.x2_park = SRT_X2_PARK;
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
@@ -157,14 +170,15 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
                                          : pick_extend<512>(dev->counters, mode);
     plan.fn = (const void*)fn;
   }
-  {   // SRT_WF_SHADE=1: one thread per slot; 2 (default): sorted passes over 512-slot chunks
-    const char* sh = tune_env("SRT_WF_SHADE");
-    const bool sorted = !(sh && atoi(sh) == 1);
+  {   // SRT_WF_SHADE=1: one thread per slot; 2: sorted passes over 512-slot chunks; 3: the same with carried remainders
+    int kind = SRT_SHADE_DEFAULT;
+    if (const char* sh = tune_env("SRT_WF_SHADE")) { const int v = atoi(sh); if (v >= 1 && v <= 3) kind = v; }
     int ts = SRT_SHADE2_THREADS;
     if (const char* t = tune_env("SRT_WF_SHADE_THREADS")) ts = atoi(t) == 128 ? 128 : 256;
-    plan.wf_shade_threads = sorted ? ts : 256;
-    plan.wf_shade_chunk = sorted ? 2 * ts : 256;
-    if (!sorted) plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
+    plan.wf_shade_threads = kind == 2 ? ts : 256;
+    plan.wf_shade_chunk = kind == 2 ? 2 * ts : kind == 3 ? 512 : 256;
+    if (kind == 1) plan.wf_shade = dev->counters ? (const void*)k_wf_shade<true> : (const void*)k_wf_shade<false>;
+    else if (kind == 3) plan.wf_shade = dev->counters ? (const void*)k_wf_shade2c<true> : (const void*)k_wf_shade2c<false>;
     else if (ts == 128) plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 128> : (const void*)k_wf_shade2<false, 128>;
     else plan.wf_shade = dev->counters ? (const void*)k_wf_shade2<true, 256> : (const void*)k_wf_shade2<false, 256>;
   }

@@ -528,6 +528,157 @@ __global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shad
   }
 }
 
+// ---- SHADE + REGENERATE, sorted phases with carried remainders --------------------------------------------------------
+// In k_wf_shade2 a 512-slot chunk yields ~280 hits and ~290 free slots for 256 threads: the second round of passes 1 and 2
+// runs with ONE warp while seven wait at the barrier (ncu: 5.3 warps per issue stalled on the barrier, the largest stall).
+// Here the lists hold pool-wide slot numbers and outlive the chunk: a pass only serves whole rounds of 256 entries and hands
+// the remainder (< 256) to the next chunk's lists; the block's last chunk serves everything.  A slot classified in chunk c
+// may thus be shaded or regenerated while chunk c + 1 is classified - nothing else reads it before the next extend launch.
+template <bool COUNT>
+__global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2c(Scene sc, RenderArgs A, WfPool pool, WfCursors* cur, float* __restrict__ accum,
+                                                    unsigned long long* counters) {
+  constexpr int TS = 256, CH = 512;
+  constexpr int CAP_H = CH + TS;                // carried (< TS) + this chunk's hits (<= CH)
+  constexpr int CAP_F = 2 * CH + 2 * TS;        // carried + this chunk's free slots + the paths pass 1 ended (<= CAP_H)
+  __shared__ unsigned s_hit[2][CAP_H], s_free[2][CAP_F];
+  __shared__ unsigned s_nhit[2], s_nfree[2];
+  __shared__ unsigned long long s_base;
+  __shared__ unsigned long long s_stat[3];
+  const int lane = threadIdx.x & 31;
+  const unsigned FULL = 0xffffffffu, below = (1u << lane) - 1;
+  if (blockIdx.x == 0 && threadIdx.x == 0) cur->ray = 0;    // the next extend wave starts at slot 0
+  if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+  if (threadIdx.x < 2) { s_nhit[threadIdx.x] = 0; s_nfree[threadIdx.x] = 0; }
+  const unsigned long long per_sample = (unsigned long long)A.n_tiles * 32ull;
+  const unsigned long long total = per_sample * (unsigned long long)A.sample_count;
+  Counters cnt = {0, 0, 0, 0, 0};
+  unsigned n_new = 0, n_seg = 0;
+  __syncthreads();
+
+  int buf = 0;
+  for (long long chunk = blockIdx.x; chunk * CH < (long long)pool.n_slots; chunk += gridDim.x, buf ^= 1) {
+    const long long base = chunk * CH;
+    const bool last = (chunk + (long long)gridDim.x) * CH >= (long long)pool.n_slots;
+#if SRT_SHADE_PREFETCH
+    {   // the block's next chunk: pull its records towards the L2 while this chunk is served (they stream from HBM)
+      const long long nb = (chunk + (long long)gridDim.x) * CH;
+      if (nb + CH <= (long long)pool.n_slots) {
+        constexpr int L16 = CH / 8, L8 = CH / 16;      // 128-byte lines: three 16-byte arrays, two 8-byte arrays
+        for (int t = threadIdx.x; t < 3 * L16 + 2 * L8; t += TS) {
+          const void* p;
+          if (t < 3 * L16) { const int a = t / L16, line = t % L16; p = (a == 0 ? pool.thr : a == 1 ? pool.ray_o : pool.ray_d) + nb + line * 8; }
+          else { const int u = t - 3 * L16, line = u % L8; p = u < L8 ? (const void*)(pool.hit + nb + line * 16) : (const void*)(pool.id + nb + line * 16); }
+          asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+        }
+      }
+    }
+#endif
+    // ---- pass 0: classify (two slots per thread, all loads first); the lists already hold the carried entries
+    float4 t4[2]; int2 h[2]; uint32_t pix[2];
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const long long k = base + q * TS + threadIdx.x;
+      t4[q] = make_float4(0, 0, 0, __int_as_float(-2)); h[q] = make_int2(-1, 0); pix[q] = 0;
+      if (k < (long long)pool.n_slots) { t4[q] = pool.thr[k]; h[q] = pool.hit[k]; pix[q] = pool.id[k].x; }
+    }
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const unsigned k = (unsigned)(base + q * TS + threadIdx.x);
+      const int bounce = __float_as_int(t4[q].w);
+      bool is_hit = false, is_free = false;
+      if (bounce == -1) is_free = true;                                    // no path in this slot (-2: beyond the pool)
+      else if (bounce >= 0) {
+        if (h[q].x < 0) {                                                  // miss -> background, main.cpp:39-40
+          float* px = accum + (size_t)pix[q] * 3;
+          atomicAdd(px, t4[q].x * A.bg[0]); atomicAdd(px + 1, t4[q].y * A.bg[1]); atomicAdd(px + 2, t4[q].z * A.bg[2]);
+          is_free = true;
+        } else is_hit = true;
+      }
+      const unsigned mh = __ballot_sync(FULL, is_hit), mf = __ballot_sync(FULL, is_free);
+      unsigned bh = 0, bf = 0;
+      if (lane == 0) { if (mh) bh = atomicAdd(&s_nhit[buf], __popc(mh)); if (mf) bf = atomicAdd(&s_nfree[buf], __popc(mf)); }
+      bh = __shfl_sync(FULL, bh, 0); bf = __shfl_sync(FULL, bf, 0);
+      if (is_hit) s_hit[buf][bh + __popc(mh & below)] = k;
+      if (is_free) s_free[buf][bf + __popc(mf & below)] = k;
+    }
+    __syncthreads();
+    // ---- pass 1: shade whole rounds of hits; the remainder moves to the next chunk's list
+    const unsigned n_hit = s_nhit[buf];
+    const unsigned do_hit = last ? n_hit : n_hit / TS * TS;
+    for (unsigned t = threadIdx.x; t < do_hit; t += TS) {
+      const unsigned k = s_hit[buf][t];
+      const float4 th4 = pool.thr[k], o = pool.ray_o[k], d = pool.ray_d[k];
+      const int2 hh = pool.hit[k];
+      const uint2 id = pool.id[k];
+      int bounce = __float_as_int(th4.w);
+      Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
+      V3 thr = mk(th4.x, th4.y, th4.z), L = mk(0, 0, 0);
+      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
+      if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                      // this segment's emitted term (NaN included)
+        float* px = accum + (size_t)id.x * 3;
+        atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
+      }
+      if (done) s_free[buf][atomicAdd(&s_nfree[buf], 1u)] = k;
+      else {
+        pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+        pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+        pool.thr[k] = make_float4(thr.x, thr.y, thr.z, __int_as_float(bounce));
+        ++n_seg;
+      }
+    }
+    if (threadIdx.x < n_hit - do_hit) s_hit[buf ^ 1][threadIdx.x] = s_hit[buf][do_hit + threadIdx.x];   // (< TS entries)
+    __syncthreads();
+    // ---- pass 2: regenerate whole rounds of free slots
+    const unsigned n_free = s_nfree[buf];
+    const unsigned do_free = last ? n_free : n_free / TS * TS;
+    if (threadIdx.x == 0) {
+      s_base = do_free ? atomicAdd(&cur->path, (unsigned long long)do_free) : total;
+      s_nhit[buf ^ 1] = n_hit - do_hit; s_nfree[buf ^ 1] = n_free - do_free;     // the next chunk's lists start with the carry
+    }
+    if (threadIdx.x < n_free - do_free) s_free[buf ^ 1][threadIdx.x] = s_free[buf][do_free + threadIdx.x];
+    __syncthreads();
+    const unsigned long long pbase = s_base;
+    for (unsigned t = threadIdx.x; t < do_free; t += TS) {
+      const unsigned k = s_free[buf][t];
+      const unsigned long long mine = pbase + t;
+      bool made = false;
+      if (mine < total) {
+        const unsigned q = (unsigned)(mine % per_sample);
+        const int s_off = (int)(mine / per_sample);
+        const int tile = (int)(q >> 5), l = (int)(q & 31);
+        const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
+        if (x < A.W && y < A.H) {
+          const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
+          const Ray r = generate_ray(A, x, y, pixel, sample);
+          pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+          pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
+          pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
+          pool.id[k] = make_uint2(pixel, sample);
+          made = true; ++n_new; ++n_seg;
+        }
+      }
+      if (!made) {                                  // no path: extend skips the slot, the next shade pass retries
+        pool.ray_d[k] = make_float4(0, 0, 0, __int_as_float(0));
+        pool.thr[k] = make_float4(0, 0, 0, __int_as_float(-1));
+      }
+    }
+    // no barrier here: the next chunk appends to the other pair of lists (whose carried part was written before the last
+    // barrier), and s_base is not written again before every thread has passed that chunk's second barrier
+  }
+  unsigned long long v0 = n_new, v1 = n_seg, v2 = cnt.tri_hits;
+  for (int o = 16; o > 0; o >>= 1) {
+    v0 += __shfl_down_sync(FULL, v0, o); v1 += __shfl_down_sync(FULL, v1, o);
+    if (COUNT) v2 += __shfl_down_sync(FULL, v2, o);
+  }
+  if (lane == 0) { atomicAdd(&s_stat[0], v0); atomicAdd(&s_stat[1], v1); if (COUNT) atomicAdd(&s_stat[2], v2); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (s_stat[0]) atomicAdd(&counters[0], s_stat[0]);
+    if (s_stat[1]) { atomicAdd(&counters[1], s_stat[1]); cur->alive = 1; }
+    if (COUNT && s_stat[2]) atomicAdd(&counters[7], s_stat[2]);
+  }
+}
+
 // ---- ray ordering for trees that live in HBM -------------------------------------------------------------------------
 // After a few bounces the rays of neighbouring slots have nothing in common, and every lane drags its own part of a 1 GB
 // scene through the L2.  Sorting the wave's rays by where they start (Morton code of the origin's cell in a 256^3 grid over

@@ -1,4 +1,4 @@
-"""A/B timing of the wavefront's launch shapes on one GPU: python tools/wf_ab.py <spp> <x2>:<threads>:<th_walk>[:<fused>[:<shade threads>[:<shade kernel 1|2>[:<park 144|160>]]]] [...]
+"""A/B timing of the wavefront's launch shapes on one GPU: python tools/wf_ab.py <spp> <x2>:<threads>:<th_walk>[:<fused>[:<shade threads>[:<shade kernel 1|2|3>[:<park 144|160>]]]] [...]
 (x2 = 0 / 16 / 32 selects k_wf_extend / k_wf_extend2 with 16- / 32-byte nodes; fused = 1: k_wf_path, one launch per frame).
 Config-4 geometry (1280x720, depth 4)."""
 import os, sys
