@@ -241,9 +241,9 @@ __device__ __forceinline__ void x2_leaf_phase(const Scene& sc, const WfPool& poo
 // (profiles/r2_extend2_ab.md): separate lists for leaves with / without a sphere make the phases 1.4 % cheaper but need 160
 // entries per warp: with 16-byte entries (209 KB, 19 KB of L1) 1.50 ms per launch against 1.385; with 8-byte entries and the
 // ray's (prim, tCur) kept in pool.hit (170 KB, the 196 KB step) 1.43-1.45.
-// HIOFF (FMT 32 only): byte offset of the hi[] half of the nodes when it is a compile-time constant (the host picks 65536
-// for trees of 2049-4096 nodes) - the second LDS.128 of a step then takes its address from the same register with an
-// immediate offset instead of an extra add per step; 0 = hi[] follows lo[] at n * 16.
+// HIOFF (FMT 32 only, A/B builds): byte offset of the hi[] half of the nodes as a compile-time constant - the second LDS.128
+// of a step then takes an immediate offset instead of an add per step.  Measured with 65536 on config 4: 1.381 vs 1.345 ms
+// per launch (lo[k] and hi[k] then sit in the same banks); the host always uses 0 = hi[] follows lo[] at n * 16.
 template <bool COUNT, int FMT, int THREADS, int HIOFF = 0>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
                                                           unsigned long long* counters) {

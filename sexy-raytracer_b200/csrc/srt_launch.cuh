@@ -52,11 +52,8 @@ path_fn pick_path(bool count, int fmt) {
   if (count) return fmt == 16 ? k_wf_path<true, 16, THREADS> : k_wf_path<true, 32, THREADS>;
   return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
 }
-#ifndef SRT_X2_HIOFF_DEFAULT
-#define SRT_X2_HIOFF_DEFAULT 1
-#endif
 #ifndef SRT_SHADE_DEFAULT
-#define SRT_SHADE_DEFAULT 2
+#define SRT_SHADE_DEFAULT 3       /* 2: k_wf_shade2, 3: k_wf_shade2c (carried remainders; -7 % per wave, B200) */
 #endif
 #ifndef SRT_SHADE2_THREADS
 #define SRT_SHADE2_THREADS 256
@@ -134,14 +131,7 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
                        : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
                                              : (const void*)pick_extend2<512>(dev->counters, fmt);
       if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
-      size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
-      // 2049-4096 nodes at the default CTA size: hi[] at the constant offset 64 KB (k_wf_extend2's HIOFF), 64 KB - n * 16 bytes more
-      const char* ho = tune_env("SRT_WF_HIOFF");
-      if (fmt == 32 && plan.threads == 1024 && s->sc.n_nodes > 2048 && s->sc.n_nodes <= 4096 && !(ho && atoi(ho) == 0) && SRT_X2_HIOFF_DEFAULT) {
-        f2 = dev->counters ? (const void*)k_wf_extend2<true, 32, 1024, 65536> : (const void*)k_wf_extend2<false, 32, 1024, 65536>;
-        need += 65536 - (size_t)s->sc.n_nodes * 16;
-        if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
-      }
+      const size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
       if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
       plan.x2_park = SRT_X2_PARK;
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;

@@ -252,6 +252,32 @@ def test_fused_path_kernel_odd_sizes_depths_and_counters(device, dev_scenes, sce
         assert ca[k] == cb[k], (k, ca[k], cb[k])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c1_shirley", "c3_masterchief"])
+def test_shade_kernels_agree(name, dev_scenes, scenes):
+    """k_wf_shade (one thread per slot), k_wf_shade2 (sorted passes per 512-slot chunk) and k_wf_shade2c (the default: lists that
+    carry their remainder to the next chunk) trace the same paths: same path and segment counts, sums equal up to fp32 order.
+    Small pools make blocks serve several chunks, so the carried lists are exercised."""
+    from test_gpu_parity import SMALL
+    s = scenes[name]
+    W, H, spp = SMALL[name]
+    kw = dict(width=W, height=H, spp=spp, seed=23, variant=2)
+    ref = None
+    for kind, wf in ((1, None), (2, None), (3, None), (3, "4096,256,8"), (3, "65536,1024,8"), (2, "4096,512,8")):
+        e = dict(SRT_WF_SHADE=kind)
+        if wf:
+            e["SRT_WF"] = wf
+        with env(**e):
+            a, _, st = dev_scenes[name].render(s.render_params(**kw), want_rgba=False)
+        if ref is None:
+            ref = (a, st)
+            continue
+        assert st.paths == ref[1].paths and st.segments == ref[1].segments, (kind, wf)
+        fin = np.isfinite(ref[0]).all(axis=2)
+        assert (np.isfinite(a).all(axis=2) == fin).all()
+        assert np.abs(a[fin] - ref[0][fin]).max() <= 2e-5 * max(1.0, np.abs(ref[0][fin]).max()), (kind, wf)
+
+
 def test_extend2_refuses_trees_it_cannot_serve(device, scenes, port):
     """a tree whose boxes are not nested keeps k_wf_extend (plan_wavefront), with the same hits"""
     import copy
