@@ -96,9 +96,9 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
   plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
   // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
-  // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, profiles/r1_logs/ai_threads.log); below 1024 the rate falls linearly
+  // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, round-1 sweep recorded in profiles/r1_c5_extend_summary.md); below 1024 the rate falls linearly
   // ... and a pool of 64 Mi slots (5.4 GB + 1 GB of sort buffers): the more rays one sort orders, the smaller the region of
-  // the scene the rays in flight cover - 8 / 32 / 64 / 128 Mi slots: 63.7 / 70.3 / 71.3 / 71.1 M segments/s (r1_logs/ap_pool.log)
+  // the scene the rays in flight cover - 8 / 32 / 64 / 128 Mi slots: 63.7 / 70.3 / 71.3 / 71.1 M segments/s (profiles/r1_c5_extend_summary.md)
   if (!s->nodes_in_smem && s->node_bytes > dev->l2_bytes) { plan.threads = 768; plan.wf_slots = 1 << 26; }
   bool wf_env = false;
   if (const char* t = tune_env("SRT_WF")) {

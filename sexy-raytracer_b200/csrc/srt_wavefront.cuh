@@ -707,7 +707,7 @@ __global__ void k_wf_keys(WfPool pool, WfSortGrid g, unsigned* __restrict__ keys
     const int cz = min(255, max(0, (int)((o.z - g.org[2]) * g.inv_cell[2])));
     const unsigned oct = (d.x < 0 ? 1u : 0u) | (d.y < 0 ? 2u : 0u) | (d.z < 0 ? 4u : 0u);
     const unsigned m8 = spread3(cx) | (spread3(cy) << 1) | (spread3(cz) << 2);
-    key = g.mode == 1 ? ((m8 << 3) | oct) : ((oct << 24) | m8);   // octant first measured 1 % ahead of cell first (r1_logs/ae_keys.log)
+    key = g.mode == 1 ? ((m8 << 3) | oct) : ((oct << 24) | m8);   // octant first measured 1 % ahead of cell first (round-1 sweep, profiles/r1_c5_extend_summary.md)
   }
   keys[k] = key;
   vals[k] = (unsigned)k;
