@@ -120,6 +120,11 @@ struct Scene {
   // coordinates are taken relative to in the walk's 16-byte nodes (median of the leaf boxes' centres)
   int x2_ok;
   float x2_centre[3];
+  // the tree k_wf_extend2 / k_wf_path walk: the same leaves in the same order under FEWER inner nodes (srt_scene_create:
+  // an inner node whose box is nearly its parent's culls too little to pay for its test and is left out - its children
+  // hang under the parent).  Same 32-byte format and threading as `nodes`; leaves are copies of the original leaf nodes.
+  const Node* x2_nodes;
+  int x2_n;
 };
 
 // ---- aabb::hit, aabb.h:11-27 --------------------------------------------------------------------

@@ -77,12 +77,12 @@ __device__ __forceinline__ float x2_hi(float c, float centre) { const float v = 
 
 __device__ __forceinline__ unsigned pack_h2(__half a, __half b) { return (unsigned)__half_as_ushort(a) | ((unsigned)__half_as_ushort(b) << 16); }
 
-// One node of the caller's threaded tree (srt_core.cuh: Node) -> the walk's record.  Links: >= 0 next node, X2_DONE, or
+// One node of the walk tree (Scene::x2_nodes: the caller's threaded tree with low-value inner nodes left out) -> the walk's record.  Links: >= 0 next node, X2_DONE, or
 // (-2 - k) = stop on leaf k.
 template <int FMT>
 __device__ __forceinline__ void x2_encode(const Scene& sc, int k, uint4* s_nodes, bool two_lists = true, int hi_index = -1) {
-  const int n = sc.n_nodes;
-  const float4 lo = __ldg(&sc.nodes[k].lo), hi = __ldg(&sc.nodes[k].hi);
+  const int n = sc.x2_n;
+  const float4 lo = __ldg(&sc.x2_nodes[k].lo), hi = __ldg(&sc.x2_nodes[k].hi);
   const int w6 = __float_as_int(hi.z), w7 = __float_as_int(hi.w);
   const bool inner = w7 == NODE_INNER;
   const int scale = FMT == 32 ? 16 : 1;
@@ -166,7 +166,7 @@ __device__ __forceinline__ bool tri_hit_nb(const Tri* __restrict__ tris, int i, 
 template <bool COUNT, bool SPH>
 __device__ __forceinline__ void x2_leaf(const Scene& sc, int node, const Ray& r, float& tCur, int& prim, Counters& cnt) {
   float4 lo, hi;
-  load_node_soa<false>(sc.nodes, 0u, 0u, node, lo, hi);
+  load_node_soa<false>(sc.x2_nodes, 0u, 0u, node, lo, hi);
   if (COUNT) ++cnt.exact;
 #if SRT_X2_NB
   if (!box_hit_exact_nb(lo, hi, r, 0.001f, tCur)) return;
@@ -248,7 +248,7 @@ template <bool COUNT, int FMT, int THREADS, int HIOFF = 0>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool, WfCursors* cur, int th_walk, int park,
                                                           unsigned long long* counters) {
   extern __shared__ uint4 smem_x2[];
-  const int n = sc.n_nodes;
+  const int n = sc.x2_n;
   for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2, false, HIOFF ? HIOFF / 16 : -1);
   const int node_u4 = FMT == 32 ? (HIOFF ? HIOFF / 16 + n : 2 * n) : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
     if (stp) {
       s_park[p + __popc(ms & below)] = make_uint4((unsigned)slot, (unsigned)(-2 - i), __float_as_uint(tCur), (unsigned)prim);
 #if SRT_X2_PREFETCH
-      asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.nodes + (-2 - i)));      // the leaf's true box + primitive ids, for the phase
+      asm volatile("prefetch.global.L1 [%0];" :: "l"(sc.x2_nodes + (-2 - i)));      // the leaf's true box + primitive ids, for the phase
 #endif
       slot = -1; i = X2_DONE;
     }

@@ -125,13 +125,13 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
     cudaFuncAttributes fa2{};
     for (int fmt : {want, want == 16 ? 32 : 0}) {
       if (fmt != 16 && fmt != 32) continue;
-      if (s->sc.n_nodes > X2_MAX_NODES(fmt)) continue;                      // links + the leaf-kind bit of the stop code
+      if (s->sc.x2_n > X2_MAX_NODES(fmt)) continue;                      // links + the leaf-kind bit of the stop code
       const void* f2 = plan.threads == 1024 ? (const void*)pick_extend2<1024>(dev->counters, fmt)
                        : plan.threads == 768 ? (const void*)pick_extend2<768>(dev->counters, fmt)
                        : plan.threads == 256 ? (const void*)pick_extend2<256>(dev->counters, fmt)
                                              : (const void*)pick_extend2<512>(dev->counters, fmt);
       if (cudaFuncGetAttributes(&fa2, f2) != cudaSuccess) { cudaGetLastError(); continue; }
-      const size_t need = x2_smem_bytes(s->sc.n_nodes, fmt, plan.threads, SRT_X2_PARK);
+      const size_t need = x2_smem_bytes(s->sc.x2_n, fmt, plan.threads, SRT_X2_PARK);
       if (need + fa2.sharedSizeBytes > dev->smem_optin) continue;
       plan.x2_park = SRT_X2_PARK;
       plan.x2_fmt = fmt; plan.fn = f2; plan.smem = need;
@@ -147,8 +147,8 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
     if (want) {
       const void* fp = plan.threads == 1024 ? (const void*)pick_path<1024>(dev->counters, plan.x2_fmt) : (const void*)pick_path<512>(dev->counters, plan.x2_fmt);
       cudaFuncAttributes fa3{};
-      const size_t need = (size_t)s->sc.n_nodes * (size_t)plan.x2_fmt + (size_t)(plan.threads / 32) * PATH_WARP_BYTES;
-      if (cudaFuncGetAttributes(&fa3, fp) == cudaSuccess && need + fa3.sharedSizeBytes <= dev->smem_optin && s->sc.n_nodes * 16ll < (1ll << 24)) {
+      const size_t need = (size_t)s->sc.x2_n * (size_t)plan.x2_fmt + (size_t)(plan.threads / 32) * PATH_WARP_BYTES;
+      if (cudaFuncGetAttributes(&fa3, fp) == cudaSuccess && need + fa3.sharedSizeBytes <= dev->smem_optin && s->sc.x2_n * 16ll < (1ll << 24)) {
         plan.fused = 1; plan.fn = fp; plan.smem = need;
       } else cudaGetLastError();
     }

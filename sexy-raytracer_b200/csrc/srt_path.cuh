@@ -161,7 +161,7 @@ template <bool COUNT, int FMT, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_wf_path(Scene sc, RenderArgs A, PathPool pool, WfCursors* cur, float* __restrict__ accum,
                                                        int th_walk, int chunk, unsigned long long* counters) {
   extern __shared__ uint4 smem_x2[];
-  const int n = sc.n_nodes;
+  const int n = sc.x2_n;
   for (int k = threadIdx.x; k < n; k += THREADS) x2_encode<FMT>(sc, k, smem_x2);
   const int node_u4 = FMT == 32 ? 2 * n : n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -397,8 +397,8 @@ def test_wavefront_agrees(name, device, dev_scenes, scenes):
         k2 = device.last_counters()
     finally:
         device.set_counters(False)
-    # k_wf_extend2 culls inner nodes conservatively: it may look at a few more boxes, never at other primitives
-    assert ca.node_visits <= cb.node_visits <= 1.02 * ca.node_visits + 64 and ca.leaf_tests == cb.leaf_tests
+    # k_wf_extend2 culls inner nodes conservatively over a tree with fewer inner nodes: other boxes, never other primitives
+    assert cb.node_visits <= 1.02 * ca.node_visits + 64 and ca.leaf_tests == cb.leaf_tests
     assert k1["sphere_leaf_tests"] == k2["sphere_leaf_tests"] and k1["triangle_hits"] == k2["triangle_hits"]
     # a slot pool smaller than the frame (many waves) and a sample sub-range give the same frame
     import os
