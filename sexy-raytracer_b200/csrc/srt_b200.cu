@@ -361,48 +361,103 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     }
   }
   // The tree k_wf_extend2 walks (Scene::x2_nodes).  Its inner nodes only cull, and they may cull conservatively (DESIGN
-  // section 4), so an inner node can also be LEFT OUT: its children are then tested whenever it would have been.  That pays when
-  // the node is hit most of the times it is tested - leaving it out saves its own test and costs two tests of children that
-  // would have been skipped, so the break-even is a hit probability of 1/2; surface-area ratio to the kept ancestor stands in
-  // for the probability.  The reference's tree (random axis, median split: bvh.h:55-95) has many such nodes - config 3/4: 54.1
-  // box tests per ray with all 2 021 inner nodes, 38.0 with the 1 220 that pass ratio <= 0.6 (same leaves, same order).  The
-  // root goes too (rays start inside it).  Leaves are copied unchanged: they carry the exact test.
+  // section 4): what has to be the reference's is the SEQUENCE of leaves and the test at each leaf.  Any hierarchy of boxes over
+  // contiguous runs of that sequence is therefore admissible - a run whose union box is certainly missed holds no leaf whose
+  // own box could be hit, and skipping it changes no tCur.  So the walk does not use the reference's inner nodes (random axis,
+  // median split: bvh.h:55-95) but its own over the same leaves, in two steps:
+  //   1. top-down over the leaf sequence, each run split where  area(left) * count(left) + area(right) * count(right)  is
+  //      smallest (a surface-area-heuristic sweep along the one order parity allows);
+  //   2. an inner node that would be hit most of the times it is tested is left out - its children hang under the kept ancestor.
+  //      Leaving it out saves its own test and costs the tests of children it would have culled: break-even at a hit
+  //      probability of 1/2, estimated by the area ratio to the kept ancestor (threshold `tau`, 0.6 measured best).  The root
+  //      goes too (rays start inside it).
+  // Config 3/4, box tests per ray (CPU model over primary + secondary rays, profiles/r2_walk_tree.md): reference tree 55.3,
+  // step 2 alone on the reference's inner nodes 39.2, step 1 alone 32.5, both 26.5.  Leaves are copied unchanged.
   std::vector<Node> x2nodes;
   s->sc.x2_nodes = nullptr; s->sc.x2_n = 0;
   if (s->sc.x2_ok) {
     float tau = 0.6f;
-    if (const char* t = getenv("SRT_DEBUG_TUNING")) if (!strcmp(t, "1")) if (const char* v = getenv("SRT_X2_TAU")) tau = (float)atof(v);
+    int rebuild = 1;
+    if (const char* t = getenv("SRT_DEBUG_TUNING")) if (!strcmp(t, "1")) {
+      if (const char* v = getenv("SRT_X2_TAU")) tau = (float)atof(v);
+      if (const char* v = getenv("SRT_X2_SAH")) rebuild = atoi(v);
+    }
     auto w7_of = [&](int i) { int32_t w; memcpy(&w, &nodes[i].hi.w, 4); return w; };
     auto w6_of = [&](int i) { int32_t w; memcpy(&w, &nodes[i].hi.z, 4); return w; };
-    auto area = [&](int i) {
-      const double dx = std::max(0.0, (double)nodes[i].lo.w - nodes[i].lo.x), dy = std::max(0.0, (double)nodes[i].hi.x - nodes[i].lo.y),
-                   dz = std::max(0.0, (double)nodes[i].hi.y - nodes[i].lo.z);
+    struct Box { float lo[3], hi[3]; };
+    auto box_of = [&](int i) { Box b = {{nodes[i].lo.x, nodes[i].lo.y, nodes[i].lo.z}, {nodes[i].lo.w, nodes[i].hi.x, nodes[i].hi.y}}; return b; };
+    auto grow = [](Box& a, const Box& b) { for (int k = 0; k < 3; k++) { a.lo[k] = std::min(a.lo[k], b.lo[k]); a.hi[k] = std::max(a.hi[k], b.hi[k]); } };
+    auto area = [](const Box& b) {
+      const double dx = std::max(0.0, (double)b.hi[0] - b.lo[0]), dy = std::max(0.0, (double)b.hi[1] - b.lo[1]), dz = std::max(0.0, (double)b.hi[2] - b.lo[2]);
       return 2.0 * (dx * dy + dy * dz + dz * dx);
     };
-    struct Kept { int end; double sa; };
-    std::vector<Kept> anc;                       // kept inner ancestors of the node at hand
-    std::vector<int> skip_orig;                  // per emitted node: original index its skip link points at (inner nodes)
-    std::vector<int> first_at(n_real + 1, -1);   // original index -> position of the first emitted node at or after it
-    for (int i = 0; i < n_real; i++) {
-      while (!anc.empty() && i >= anc.back().end) anc.pop_back();
-      const bool inner = w7_of(i) == NODE_INNER;
-      if (inner) {
-        const double sa = area(i);
-        const bool drop = tau < 1.0f && n_real > 1 &&
-                          (anc.empty() ? i == 0 : (anc.back().sa > 0.0 && std::isfinite(sa) && sa / anc.back().sa > (double)tau));
-        if (drop) continue;
-        anc.push_back({w6_of(i), sa});
+    auto inner_node = [&](const Box& b) {
+      Node nd; nd.lo = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]); nd.hi = make_float4(b.hi[1], b.hi[2], 0.f, i2f(NODE_INNER)); return nd;
+    };
+    if (rebuild) {
+      std::vector<int> leaves;                               // the leaf nodes in the reference's order
+      for (int i = 0; i < n_real; i++) if (w7_of(i) != NODE_INNER) leaves.push_back(i);
+      const int L = (int)leaves.size();
+      std::vector<Box> lb((size_t)L), suf((size_t)L);
+      for (int k = 0; k < L; k++) lb[k] = box_of(leaves[k]);
+      struct Job { int a, b; double anc_sa; int close; };     // close >= 0: "subtree of emitted node `close` ends here"
+      std::vector<Job> st;
+      st.push_back({0, L, -1.0, -1});
+      bool top = true;
+      while (!st.empty()) {
+        const Job j = st.back(); st.pop_back();
+        if (j.close >= 0) { x2nodes[j.close].hi.z = i2f((int32_t)x2nodes.size()); continue; }
+        if (j.b - j.a == 1) { x2nodes.push_back(nodes[leaves[j.a]]); top = false; continue; }
+        // suffix boxes of the run, then the sweep
+        suf[j.b - 1] = lb[j.b - 1];
+        for (int k = j.b - 2; k >= j.a; k--) { suf[k] = lb[k]; grow(suf[k], suf[k + 1]); }
+        Box pre = lb[j.a];
+        double best = std::numeric_limits<double>::infinity();
+        int cut = j.a + 1;
+        for (int k = j.a + 1; k < j.b; k++) {                 // left = [a, k), right = [k, b)
+          const double c = area(pre) * (k - j.a) + area(suf[k]) * (j.b - k);
+          if (c < best) { best = c; cut = k; }
+          grow(pre, lb[k]);
+        }
+        const Box all = suf[j.a];
+        const double sa = area(all);
+        const bool drop = tau < 1.0f && (top || (j.anc_sa > 0.0 && std::isfinite(sa) && sa / j.anc_sa > (double)tau));
+        double child_anc = j.anc_sa;
+        if (!drop) {
+          const int pos = (int)x2nodes.size();
+          x2nodes.push_back(inner_node(all));
+          st.push_back({0, 0, 0.0, pos});
+          child_anc = sa;
+        }
+        top = false;
+        st.push_back({cut, j.b, child_anc, -1});
+        st.push_back({j.a, cut, child_anc, -1});
       }
-      first_at[i] = (int)x2nodes.size();
-      x2nodes.push_back(nodes[i]);
-      skip_orig.push_back(inner ? w6_of(i) : -1);
+    } else {                                                  // step 2 on the reference's own inner nodes (A/B runs)
+      struct Kept { int end; double sa; };
+      std::vector<Kept> anc;
+      std::vector<int> skip_orig;
+      std::vector<int> first_at(n_real + 1, -1);
+      for (int i = 0; i < n_real; i++) {
+        while (!anc.empty() && i >= anc.back().end) anc.pop_back();
+        const bool inner = w7_of(i) == NODE_INNER;
+        if (inner) {
+          const double sa = area(box_of(i));
+          const bool drop = tau < 1.0f && n_real > 1 &&
+                            (anc.empty() ? i == 0 : (anc.back().sa > 0.0 && std::isfinite(sa) && sa / anc.back().sa > (double)tau));
+          if (drop) continue;
+          anc.push_back({w6_of(i), sa});
+        }
+        first_at[i] = (int)x2nodes.size();
+        x2nodes.push_back(nodes[i]);
+        skip_orig.push_back(inner ? w6_of(i) : -1);
+      }
+      first_at[n_real] = (int)x2nodes.size();
+      for (int i = n_real - 1; i >= 0; i--) if (first_at[i] < 0) first_at[i] = first_at[i + 1];
+      for (size_t k = 0; k < x2nodes.size(); k++)
+        if (skip_orig[k] >= 0) x2nodes[k].hi.z = i2f(first_at[std::min(skip_orig[k], n_real)]);
     }
-    const int m = (int)x2nodes.size();
-    first_at[n_real] = m;
-    for (int i = n_real - 1; i >= 0; i--) if (first_at[i] < 0) first_at[i] = first_at[i + 1];
-    for (int k = 0; k < m; k++)
-      if (skip_orig[k] >= 0) x2nodes[k].hi.z = i2f(first_at[std::min(skip_orig[k], n_real)]);
-    s->sc.x2_n = m;
+    s->sc.x2_n = (int)x2nodes.size();
     arena.add(x2nodes, &s->sc.x2_nodes);
   }
   if (const char* t = getenv("SRT_DEBUG_TUNING")) if (!strcmp(t, "1"))

@@ -281,10 +281,11 @@ def test_shade_kernels_agree(name, dev_scenes, scenes):
 
 
 @pytest.mark.gpu
-def test_walk_tree_collapse(device, scenes, port):
-    """Scene::x2_nodes: with every inner node kept (SRT_X2_TAU=9) the conservative walk looks at the reference's boxes or a
-    few more; with the default (inner nodes whose surface area exceeds 0.6 of their kept ancestor's are left out, the root
-    too) at clearly fewer - and at exactly the same leaves and primitives either way."""
+def test_walk_tree(device, scenes, port):
+    """Scene::x2_nodes, the tree k_wf_extend2 walks.  With the reference's own inner nodes, all kept (SRT_X2_SAH=0, SRT_X2_TAU=9)
+    the conservative walk looks at the reference's boxes or a few more.  The default - a surface-area sweep over the reference's
+    leaf sequence, then inner nodes with an area ratio above 0.6 left out - looks at about half as many, and at exactly the
+    same leaves and primitives: same ids, same leaf-test counters."""
     s = scenes["c3_masterchief"]
     h = port.from_scene(s)
     try:
@@ -294,23 +295,32 @@ def test_walk_tree_collapse(device, scenes, port):
     finally:
         port.free(h)
     out = {}
-    for tau in ("9", "0.9", "0.6", "0.3"):
-        with env(SRT_X2_TAU=tau):
+    for key, sah, tau in (("ref", 0, "9"), ("ref+collapse", 0, "0.6"), ("sah", 1, "9"), ("default", 1, "0.6"), ("sah 0.3", 1, "0.3")):
+        with env(SRT_X2_TAU=tau, SRT_X2_SAH=sah):
             ds = device.upload(s)
         try:
             device.set_counters(True)
-            prim, t = ds.trace_wavefront(rays)
-            out[tau] = device.last_counters()
+            for x2 in (32, 16):
+                with env(SRT_WF_X2=x2):
+                    prim, t = ds.trace_wavefront(rays)
+                assert (prim == want["prim"]).all(), (key, x2)
+            with env(SRT_WF_X2=32):
+                prim, t = ds.trace_wavefront(rays)
+            out[key] = device.last_counters()
         finally:
             device.set_counters(False)
             ds.close()
-        assert (prim == want["prim"]).all(), tau
-    for tau in out:
-        assert out[tau]["leaf_tests"] == out["9"]["leaf_tests"] and out[tau]["sphere_leaf_tests"] == out["9"]["sphere_leaf_tests"], tau
-    assert box <= out["9"]["node_visits"] <= 1.02 * box + 64
-    assert out["0.6"]["node_visits"] < 0.85 * box, (out["0.6"]["node_visits"], box)
-    print("box tests per ray: reference %.1f, walk tree tau 9 / 0.9 / 0.6 / 0.3: %s" %
-          (box / len(rays), " / ".join("%.1f" % (out[k]["node_visits"] / len(rays)) for k in ("9", "0.9", "0.6", "0.3"))))
+    for key in out:
+        assert out[key]["leaf_tests"] == out["ref"]["leaf_tests"] and out[key]["sphere_leaf_tests"] == out["ref"]["sphere_leaf_tests"], key
+    assert box <= out["ref"]["node_visits"] <= 1.02 * box + 64
+    assert out["ref+collapse"]["node_visits"] < 0.85 * box
+    assert out["default"]["node_visits"] < 0.65 * box, (out["default"]["node_visits"], box)
+    msg = "box tests per ray: reference %.1f; walk tree %s" % (box / len(rays), ", ".join("%s %.1f" % (k, out[k]["node_visits"] / len(rays)) for k in out))
+    print(msg)
+    path = os.environ.get("SRT_TEST_REPORT")
+    if path:
+        with open(path, "a") as f:
+            f.write(msg + "\n")
 
 
 def test_extend2_refuses_trees_it_cannot_serve(device, scenes, port):
