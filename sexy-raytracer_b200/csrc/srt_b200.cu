@@ -374,7 +374,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
   // Config 3/4, box tests per ray (CPU model over primary + secondary rays, profiles/r2_walk_tree.md): reference tree 55.3,
   // step 2 alone on the reference's inner nodes 39.2, step 1 alone 32.5, both 26.5.  Leaves are copied unchanged.
   std::vector<Node> x2nodes;
-  s->sc.x2_nodes = nullptr; s->sc.x2_n = 0;
+  s->sc.x2_nodes = nullptr; s->sc.x2_n = 0; s->sc.x2_cnodes = nullptr;
   if (s->sc.x2_ok) {
     float tau = 0.6f;
     int rebuild = 1;
@@ -408,18 +408,37 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
         const Job j = st.back(); st.pop_back();
         if (j.close >= 0) { x2nodes[j.close].hi.z = i2f((int32_t)x2nodes.size()); continue; }
         if (j.b - j.a == 1) { x2nodes.push_back(nodes[leaves[j.a]]); top = false; continue; }
-        // suffix boxes of the run, then the sweep
-        suf[j.b - 1] = lb[j.b - 1];
-        for (int k = j.b - 2; k >= j.a; k--) { suf[k] = lb[k]; grow(suf[k], suf[k + 1]); }
-        Box pre = lb[j.a];
+        // the sweep: every position of a short run; of a long run (trees of millions of leaves) 128 evenly spaced ones
+        const int len = j.b - j.a;
         double best = std::numeric_limits<double>::infinity();
         int cut = j.a + 1;
-        for (int k = j.a + 1; k < j.b; k++) {                 // left = [a, k), right = [k, b)
-          const double c = area(pre) * (k - j.a) + area(suf[k]) * (j.b - k);
-          if (c < best) { best = c; cut = k; }
-          grow(pre, lb[k]);
+        Box all;
+        if (len <= 4096) {
+          suf[j.b - 1] = lb[j.b - 1];
+          for (int k = j.b - 2; k >= j.a; k--) { suf[k] = lb[k]; grow(suf[k], suf[k + 1]); }
+          Box pre = lb[j.a];
+          for (int k = j.a + 1; k < j.b; k++) {               // left = [a, k), right = [k, b)
+            const double c = area(pre) * (k - j.a) + area(suf[k]) * (j.b - k);
+            if (c < best) { best = c; cut = k; }
+            grow(pre, lb[k]);
+          }
+          all = suf[j.a];
+        } else {
+          constexpr int NB = 128;
+          Box bin[NB], bsuf[NB];
+          int edge[NB + 1];
+          for (int q = 0; q <= NB; q++) edge[q] = j.a + (int)((long long)len * q / NB);
+          for (int q = 0; q < NB; q++) { bin[q] = lb[edge[q]]; for (int k = edge[q] + 1; k < edge[q + 1]; k++) grow(bin[q], lb[k]); }
+          bsuf[NB - 1] = bin[NB - 1];
+          for (int q = NB - 2; q >= 0; q--) { bsuf[q] = bin[q]; grow(bsuf[q], bsuf[q + 1]); }
+          Box pre = bin[0];
+          for (int q = 1; q < NB; q++) {
+            const double c = area(pre) * (edge[q] - j.a) + area(bsuf[q]) * (j.b - edge[q]);
+            if (c < best) { best = c; cut = edge[q]; }
+            grow(pre, bin[q]);
+          }
+          all = bsuf[0];
         }
-        const Box all = suf[j.a];
         const double sa = area(all);
         const bool drop = tau < 1.0f && (top || (j.anc_sa > 0.0 && std::isfinite(sa) && sa / j.anc_sa > (double)tau));
         double child_anc = j.anc_sa;
@@ -458,6 +477,10 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
         if (skip_orig[k] >= 0) x2nodes[k].hi.z = i2f(first_at[std::min(skip_orig[k], n_real)]);
     }
     s->sc.x2_n = (int)x2nodes.size();
+    {  // the same sentinel + padding as `nodes` carries (k_wf_extend walks this tree too when it lives in HBM)
+      Node t; t.lo = make_float4(0, 0, 0, 0); t.hi = make_float4(0, 0, i2f(-1), i2f(NODE_NO_BOX));
+      for (int k = 0; k < 4; k++) x2nodes.push_back(t);
+    }
     arena.add(x2nodes, &s->sc.x2_nodes);
   }
   if (const char* t = getenv("SRT_DEBUG_TUNING")) if (!strcmp(t, "1"))
@@ -465,7 +488,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
 
   // compact tree + leaf-ordered primitives for trees that stay in HBM (srt_core.cuh)
   std::vector<int32_t> lp_src;            // leaf order -> original primitive id
-  std::vector<uint4> cn;
+  std::vector<uint4> cn, cn2;
   bool have_cn = false;
   s->sc.cnodes = nullptr; s->sc.lprims = nullptr;
   if (!s->nodes_in_smem && filter_ok && n_real > 0 && d->n_tri + d->n_sph < (int64_t)CNODE_NO_PRIM - 1) {
@@ -479,7 +502,6 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       s->sc.q_org[k] = rlo[k]; s->sc.q_cell[k] = c;
       org[k] = rlo[k]; cell[k] = c;
     }
-    cn.resize(nodes.size());
     auto snap = [&](double v, int k, bool up) -> uint32_t {
       double g = (v - org[k]) / cell[k];
       g = up ? std::ceil(g) : std::floor(g);
@@ -488,8 +510,10 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       return (uint32_t)g;
     };
     bool ok = true;
-    for (size_t i = 0; i < nodes.size(); i++) {
-      const Node& nd = nodes[i];
+    auto make_compact = [&](const std::vector<Node>& src, std::vector<uint4>& cn, std::vector<int32_t>& lp_src) {
+    cn.resize(src.size());
+    for (size_t i = 0; i < src.size(); i++) {
+      const Node& nd = src[i];
       int32_t w6, w7; memcpy(&w6, &nd.hi.z, 4); memcpy(&w7, &nd.hi.w, 4);
       uint4 q = make_uint4(0, 0, 0, 0);
       if (w7 != NODE_NO_BOX) {
@@ -515,8 +539,15 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       }
       cn[i] = q;
     }
+    };
+    make_compact(nodes, cn, lp_src);
     if (ok && !lp_src.empty()) { arena.add(cn, &s->sc.cnodes); have_cn = true; }
     else lp_src.clear();
+    if (have_cn && s->sc.x2_ok && !x2nodes.empty()) {     // the walk tree's compact image: same leaves in the same order, so the
+      std::vector<int32_t> lp2;                           // leaf words come out as the same indices into lprims
+      make_compact(x2nodes, cn2, lp2);
+      if (ok && lp2 == lp_src) arena.add(cn2, &s->sc.x2_cnodes);
+    }
   }
 
   std::vector<Tri> tris((size_t)d->n_tri);

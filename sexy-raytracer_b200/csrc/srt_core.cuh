@@ -125,6 +125,7 @@ struct Scene {
   // hang under the parent).  Same 32-byte format and threading as `nodes`; leaves are copies of the original leaf nodes.
   const Node* x2_nodes;
   int x2_n;
+  const uint4* x2_cnodes;   // the compact image of x2_nodes (trees in HBM), or nullptr; leaf words index the same lprims
 };
 
 // ---- aabb::hit, aabb.h:11-27 --------------------------------------------------------------------

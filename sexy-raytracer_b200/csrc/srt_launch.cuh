@@ -43,6 +43,7 @@ struct RenderPlan {
   RenderArgs A; int blocks, threads; size_t smem; int variant; PhaseTune tune; const void* fn;
   int wf_slots, wf_th_walk, wf_shade_chunk, wf_shade_threads; const void* wf_shade;     // variant 2
   int x2_fmt, x2_park;                                                // variant 2 with k_wf_extend2: node bytes (0 = k_wf_extend), entries per warp
+  int wf_walk;                                                        // k_wf_extend over a tree in HBM walks Scene::x2_nodes / x2_cnodes
   int fused, path_chunk;                                              // variant 2 as ONE launch of k_wf_path (srt_path.cuh); path ids per atomic
 };
 
@@ -116,6 +117,11 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   if (tree && !strcmp(tree, "full")) compact = false;
   if (tree && !strcmp(tree, "compact")) compact = s->sc.cnodes != nullptr;
   const int mode = s->nodes_in_smem ? 0 : compact ? 2 : 1;
+  // Trees in HBM: k_wf_extend's exact (filtered) box test is also a conservative one, so it can walk the scene's walk tree
+  // (Scene::x2_nodes: a surface-area sweep over the reference's leaf sequence, srt_scene_create) instead of the reference's
+  // inner nodes - same leaves, same order, same hits, about half the nodes to fetch.  SRT_WF_WALKTREE=0: the reference's tree.
+  plan.wf_walk = mode != 0 && s->sc.x2_ok && s->sc.x2_nodes && (mode == 1 || s->sc.x2_cnodes);
+  if (const char* w = tune_env("SRT_WF_WALKTREE")) if (atoi(w) == 0) plan.wf_walk = 0;
   // Tree in shared memory: k_wf_extend2 (conservative walk + parked leaf tests, srt_extend2.cuh) whenever the scene allows
   // it and its nodes + park lists fit; 16-byte nodes first (half the shared-memory wavefronts per step), 32-byte otherwise.
   plan.x2_fmt = 0; plan.x2_park = SRT_X2_PARK;
@@ -314,8 +320,10 @@ srt_status run_wavefront(srt_scene* s, const RenderPlan& plan, float* accum_dev,
   int th_walk = plan.wf_th_walk;
   void* shade_args[] = {&sc, &A, &pool, &cur, &accum_dev, &ctr};
   int x2_park = plan.x2_park;
-  void* extend_args_v1[] = {&sc, &pool, &cur, &th_walk, &ctr};
-  void* extend_args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
+  Scene sce = sc;                                      // what the extend kernel walks
+  if (plan.wf_walk) { sce.nodes = sc.x2_nodes; sce.n_nodes = sc.x2_n; if (sc.x2_cnodes) sce.cnodes = sc.x2_cnodes; }
+  void* extend_args_v1[] = {&sce, &pool, &cur, &th_walk, &ctr};
+  void* extend_args_x2[] = {&sce, &pool, &cur, &th_walk, &x2_park, &ctr};
   void** extend_args = plan.x2_fmt ? extend_args_x2 : extend_args_v1;
   const unsigned reset_blocks = (unsigned)((N + 255) / 256);
   unsigned shade_blocks = (unsigned)dev->sm_count * 2 * SRT_SHADE_MIN_BLOCKS * (256 / plan.wf_shade_threads);   // persistent: resident CTAs per SM x two rounds
@@ -600,6 +608,7 @@ srt_status srt_trace_rays_wavefront(srt_scene* s, const srt_ray* rays, int64_t n
     pool.order = vals_out;
   }
   Scene sc = s->sc; WfCursors* cur = dcur.as<WfCursors>(); unsigned long long* ctr = dev->d_counters;
+  if (plan.wf_walk) { sc.nodes = sc.x2_nodes; sc.n_nodes = sc.x2_n; if (sc.x2_cnodes) sc.cnodes = sc.x2_cnodes; }
   int th_walk = plan.wf_th_walk, x2_park = plan.x2_park;
   void* args_v1[] = {&sc, &pool, &cur, &th_walk, &ctr};
   void* args_x2[] = {&sc, &pool, &cur, &th_walk, &x2_park, &ctr};
