@@ -400,6 +400,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       const int L = (int)leaves.size();
       std::vector<Box> lb((size_t)L), suf((size_t)L);
       for (int k = 0; k < L; k++) lb[k] = box_of(leaves[k]);
+      const int exact_len = L <= (1 << 16) ? L : 64;
       struct Job { int a, b; double anc_sa; int close; };     // close >= 0: "subtree of emitted node `close` ends here"
       std::vector<Job> st;
       st.push_back({0, L, -1.0, -1});
@@ -408,12 +409,13 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
         const Job j = st.back(); st.pop_back();
         if (j.close >= 0) { x2nodes[j.close].hi.z = i2f((int32_t)x2nodes.size()); continue; }
         if (j.b - j.a == 1) { x2nodes.push_back(nodes[leaves[j.a]]); top = false; continue; }
-        // the sweep: every position of a short run; of a long run (trees of millions of leaves) 128 evenly spaced ones
+        // the sweep: every position of the run; in trees of millions of leaves only runs of up to 64 leaves are swept
+        // position by position, longer ones at up to 128 evenly spaced positions (4x cheaper per leaf and level)
         const int len = j.b - j.a;
         double best = std::numeric_limits<double>::infinity();
         int cut = j.a + 1;
         Box all;
-        if (len <= 4096) {
+        if (len <= exact_len) {
           suf[j.b - 1] = lb[j.b - 1];
           for (int k = j.b - 2; k >= j.a; k--) { suf[k] = lb[k]; grow(suf[k], suf[k + 1]); }
           Box pre = lb[j.a];
@@ -424,9 +426,10 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
           }
           all = suf[j.a];
         } else {
-          constexpr int NB = 128;
-          Box bin[NB], bsuf[NB];
-          int edge[NB + 1];
+          constexpr int NBMAX = 128;
+          const int NB = std::min(NBMAX, len / 4);
+          Box bin[NBMAX], bsuf[NBMAX];
+          int edge[NBMAX + 1];
           for (int q = 0; q <= NB; q++) edge[q] = j.a + (int)((long long)len * q / NB);
           for (int q = 0; q < NB; q++) { bin[q] = lb[edge[q]]; for (int k = edge[q] + 1; k < edge[q + 1]; k++) grow(bin[q], lb[k]); }
           bsuf[NB - 1] = bin[NB - 1];

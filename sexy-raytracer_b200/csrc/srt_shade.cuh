@@ -2,10 +2,22 @@
 // Reference: hittable.h:9-22, sphere.h:32-38,73-81,96-106, model.h:156-178,214-235, texture.h,
 // material.h, pbr.h, camera.h:40-50.  Compiled with -fmad=false (see srt_core.cuh).
 #pragma once
+#ifndef SRT_SMALL_CODE
+#define SRT_SMALL_CODE 0   /* A/B builds: 1 = sinf and philox as out-of-line functions (one copy each in the shade kernels' instruction stream) */
+#endif
 #include "srt_core.cuh"
 #include "../../include/srt.h"
 
 namespace srt {
+
+#if SRT_SMALL_CODE
+__device__ __noinline__ float sinf_once(float v) { return sinf(v); }
+#define SRT_SINF sinf_once
+#define SRT_PHILOX_INLINE __device__ __noinline__
+#else
+#define SRT_SINF sinf
+#define SRT_PHILOX_INLINE __device__ __forceinline__
+#endif
 
 struct Rec {
   V3 p, normal, tangent, bitangent;
@@ -138,7 +150,7 @@ __device__ __forceinline__ V3 texture_value(const Scene& sc, int id, float u, fl
   int kind = __ldg(&t->kind);
   float scale = 1.0f;
   if (kind == SRT_TEX_CHECKER) {                                          // texture.h:42-48
-    float sines = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
+    float sines = SRT_SINF(10.0f * p.x) * SRT_SINF(10.0f * p.y) * SRT_SINF(10.0f * p.z);
     t = &sc.texs[sines < 0 ? __ldg(&t->odd) : __ldg(&t->even)];
     kind = __ldg(&t->kind);
     scale = 255.0f;
@@ -253,7 +265,7 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
 }
 
 // ---- random numbers (new: per-(pixel, sample) Philox4x32-10; DESIGN.md "random numbers") --------
-__device__ __forceinline__ uint4 philox(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
+SRT_PHILOX_INLINE uint4 philox(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
   uint32_t c0 = pixel, c1 = sample, c2 = block, c3 = 0;
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll

@@ -23,7 +23,7 @@ for cfg in sys.argv[2:]:
     if len(f) > 6: os.environ["SRT_WF_PARK"] = f[6]
     else: os.environ.pop("SRT_WF_PARK", None)
     os.environ["SRT_WF_X2"] = x2
-    os.environ["SRT_WF"] = "8388608,%s,%s" % (th, walk)
+    os.environ["SRT_WF"] = "%s,%s,%s" % (os.environ.get("AB_SLOTS", "8388608"), th, walk)
     ds.render(P, want_sum=False, want_rgba=False)
     best = None
     for _ in range(3):
