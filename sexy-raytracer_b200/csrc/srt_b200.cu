@@ -53,6 +53,7 @@ struct srt_device {
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
   void* d_path = nullptr; size_t path_capacity = 0;  // k_wf_path's warp-private path slots (srt_path.cuh)
+  int async_alloc = 0;                             // scene arenas through cudaMallocAsync / cudaFreeAsync on `stream`
   void* h_stage = nullptr; size_t h_stage_cap = 0;  // pinned staging of srt_scene_create's arena (scenes up to SCENE_STAGE_MAX bytes)
 };
 static const int WF_RING = 8;
@@ -62,6 +63,7 @@ struct srt_scene {
   srt_device* dev = nullptr;
   Scene sc{};
   std::vector<void*> buffers;
+  int async_alloc = 0;
   int64_t bytes = 0;
   int nodes_in_smem = 0;
   size_t node_bytes = 0;
@@ -102,6 +104,15 @@ srt_status srt_device_create(int gpu_id, srt_device** out) try {
   CK(cudaEventCreate(&d->ev0));
   CK(cudaEventCreate(&d->ev1));
   CK(cudaMalloc(&d->d_counters, 8 * sizeof(unsigned long long)));
+  {  // scene arenas come from the device's stream-ordered pool and go back to it (cudaMallocAsync / cudaFreeAsync): a scene per
+     // frame - the reference's flow - then costs no cudaFree, which took 1-200 ms on this pool's boxes.  Keep what was freed.
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, gpu_id) == cudaSuccess && pool) {
+      uint64_t keep = UINT64_MAX;
+      if (cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep) == cudaSuccess) d->async_alloc = 1;
+    }
+    cudaGetLastError();
+  }
   *out = d;
   return SRT_OK;
 } catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
@@ -231,7 +242,8 @@ struct SceneArena {
   // caller between alloc and upload)
   srt_status alloc(srt_scene* s) {
     void* b = nullptr;
-    cudaError_t e = cudaMalloc(&b, total ? total : 256);
+    cudaError_t e = s->dev->async_alloc ? cudaMallocAsync(&b, total ? total : 256, s->dev->stream) : cudaMalloc(&b, total ? total : 256);
+    s->async_alloc = s->dev->async_alloc;
     if (e != cudaSuccess) { cudaGetLastError(); return fail(e == cudaErrorMemoryAllocation ? SRT_ERR_NOMEM : SRT_ERR_CUDA, cudaGetErrorString(e)); }
     s->buffers.push_back(b);
     base = static_cast<char*>(b);
@@ -277,7 +289,8 @@ extern "C" {
 void srt_scene_destroy(srt_scene* s) {
   if (!s) return;
   cudaSetDevice(s->dev->gpu);
-  for (auto p : s->buffers) cudaFree(p);
+  // (every call that used the scene has synchronised its stream before it returned)
+  for (auto p : s->buffers) { if (s->async_alloc) cudaFreeAsync(p, s->dev->stream); else cudaFree(p); }
   delete s;
 }
 
