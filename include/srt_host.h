@@ -55,6 +55,12 @@ srt_status srt_png_read_memory(const uint8_t* file_bytes, int64_t len, int32_t r
 srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, const uint8_t* pixels, int32_t stride_bytes);
 void       srt_host_free(void* p);
 
+/* ---- raw radiance dump for parity tooling: Portable Float Map, colour ("PF"), little endian.
+ * `rgb` = width*height*3 floats, row 0 = TOP (the layout of srt_render's out_sum_rgb); `scale` multiplies every value on the
+ * way out (1 / spp turns the sums into mean radiance).  PFM stores rows bottom-up: the writer flips, the reader flips back. */
+srt_status srt_pfm_write(const char* path, int32_t width, int32_t height, const float* rgb, float scale);
+srt_status srt_pfm_read(const char* path, int32_t* out_width, int32_t* out_height, float** out_rgb);   /* free with srt_host_free */
+
 /* ---- checkpoint of a progressive render: the fp32 sum buffer + how many samples per pixel it holds.
  * File: "SRTF" u32 version (1; write2: 2), i32 width, height, samples_done, u64 seed, then width*height*3 little-endian floats.   */
 srt_status srt_checkpoint_write(const char* path, int32_t width, int32_t height, int32_t samples_done, uint64_t seed,

@@ -184,6 +184,26 @@ def png_write(path, pixels):
     _check(L.srt_png_write(os.fsencode(path), a.shape[1], a.shape[0], a.shape[2], a.ctypes.data_as(C.c_void_p), 0))
 
 
+def pfm_write(path, rgb, scale=1.0):
+    """srt_pfm_write: fp32 radiance [h, w, 3], row 0 = top, as a little-endian colour PFM (values times `scale`)."""
+    L = _bind_world(lib())
+    a = np.ascontiguousarray(rgb, np.float32)
+    L.srt_pfm_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_void_p, C.c_float]
+    _check(L.srt_pfm_write(os.fsencode(path), a.shape[1], a.shape[0], a.ctypes.data_as(C.c_void_p), scale))
+
+
+def pfm_read(path):
+    """srt_pfm_read -> float32 [h, w, 3], row 0 = top."""
+    L = _bind_world(lib())
+    w, h, p = C.c_int32(), C.c_int32(), C.c_void_p()
+    L.srt_pfm_read.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]
+    _check(L.srt_pfm_read(os.fsencode(path), C.byref(w), C.byref(h), C.byref(p)))
+    try:
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), (h.value, w.value, 3)).copy()
+    finally:
+        L.srt_host_free(p)
+
+
 def checkpoint_write(path, sum_rgb, samples_done, seed=1):
     """srt_checkpoint_write: the film of a progressive render (fp32 sums [h, w, 3] + samples per pixel so far)."""
     a = np.ascontiguousarray(sum_rgb, np.float32)

@@ -243,6 +243,45 @@ srt_status srt_png_write(const char* path, int32_t w, int32_t h, int32_t comp, c
 
 // Checkpoint file "SRTF": version 1 = {w, h, samples_done, seed, sums}; version 2 adds {sampler, max_bounce} after the seed so
 // that a resumed render can be refused when it would mix two sample streams (b200Device::rtFrameProgressive).
+srt_status srt_pfm_write(const char* path, int32_t w, int32_t h, const float* rgb, float scale) try {
+  if (!path || !rgb) return fail(SRT_ERR_INVALID, "NULL argument");
+  if (w <= 0 || h <= 0) return fail(SRT_ERR_INVALID, "bad image size");
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(SRT_ERR_INVALID, std::string("cannot open ") + path);
+  fprintf(f, "PF\n%d %d\n-1.0\n", w, h);                      // negative scale = little endian
+  std::vector<float> row((size_t)w * 3);
+  bool ok = true;
+  for (int y = h - 1; y >= 0 && ok; y--) {                      // PFM rows run bottom to top
+    const float* src = rgb + (size_t)y * w * 3;
+    for (size_t k = 0; k < row.size(); k++) row[k] = src[k] * scale;
+    ok = fwrite(row.data(), sizeof(float), row.size(), f) == row.size();
+  }
+  ok = (fclose(f) == 0) && ok;
+  return ok ? SRT_OK : fail(SRT_ERR_INVALID, std::string("short write to ") + path);
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
+
+srt_status srt_pfm_read(const char* path, int32_t* out_w, int32_t* out_h, float** out_rgb) try {
+  if (!path || !out_w || !out_h || !out_rgb) return fail(SRT_ERR_INVALID, "NULL argument");
+  *out_rgb = nullptr;
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(SRT_ERR_INVALID, std::string("cannot open ") + path);
+  char magic[3] = {0, 0, 0};
+  int w = 0, h = 0;
+  float scale = 0;
+  if (fscanf(f, "%2s %d %d %f", magic, &w, &h, &scale) != 4 || strcmp(magic, "PF") != 0 || fgetc(f) == EOF) { fclose(f); return fail(SRT_ERR_INVALID, "not a colour PFM file"); }
+  if (w <= 0 || h <= 0 || (int64_t)w * h > ((int64_t)1 << 28) || !(scale < 0)) { fclose(f); return fail(SRT_ERR_UNSUPPORTED, "PFM: bad size or big-endian data"); }
+  float* px = static_cast<float*>(malloc((size_t)w * h * 3 * sizeof(float)));
+  if (!px) { fclose(f); return fail(SRT_ERR_NOMEM, "out of memory"); }
+  bool ok = true;
+  for (int y = h - 1; y >= 0 && ok; y--) ok = fread(px + (size_t)y * w * 3, sizeof(float), (size_t)w * 3, f) == (size_t)w * 3;
+  fclose(f);
+  if (!ok) { free(px); return fail(SRT_ERR_INVALID, "PFM: truncated file"); }
+  const float m = -scale;
+  if (m != 1.0f) for (size_t k = 0; k < (size_t)w * h * 3; k++) px[k] *= m;
+  *out_w = w; *out_h = h; *out_rgb = px;
+  return SRT_OK;
+} catch (const std::bad_alloc&) { return fail(SRT_ERR_NOMEM, "out of memory"); } catch (const std::exception& e_) { return fail(SRT_ERR_INVALID, e_.what()); } catch (...) { return fail(SRT_ERR_INVALID, "unknown exception"); }
+
 srt_status srt_checkpoint_write2(const char* path, int32_t w, int32_t h, int32_t samples_done, uint64_t seed, int32_t sampler,
                                  int32_t max_bounce, const float* sum) try {
   if (!path || !sum || w <= 0 || h <= 0 || samples_done < 0) return fail(SRT_ERR_INVALID, "bad argument");

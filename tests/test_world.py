@@ -331,6 +331,28 @@ def test_example_renders_config1_like_the_library(tmp_path, device, dev_scenes, 
 
 
 # ---- progressive accumulation + checkpoint ----------------------------------------------------------
+def test_pfm_round_trip(tmp_path):
+    """srt_pfm_write / srt_pfm_read (a raw fp32 dump for parity tooling): values bit-exact, row 0 stays the
+    top row although the file stores rows bottom-up, the scale factor applies on the way out, the header is what other PFM
+    readers expect."""
+    rng = np.random.default_rng(3)
+    a = rng.standard_normal((7, 5, 3)).astype(np.float32) * 100
+    a[0, 0] = [np.inf, -0.0, 1e-38]
+    f = str(tmp_path / "x.pfm")
+    host.pfm_write(f, a)
+    raw = open(f, "rb").read()
+    assert raw.startswith(b"PF\n5 7\n-1.0\n")
+    body = np.frombuffer(raw[len(b"PF\n5 7\n-1.0\n"):], "<f4").reshape(7, 5, 3)
+    assert (body[::-1].view(np.uint32) == a.view(np.uint32)).all()          # bottom row first in the file
+    b = host.pfm_read(f)
+    assert b.shape == a.shape and (b.view(np.uint32) == a.view(np.uint32)).all()
+    host.pfm_write(f, a[1:], scale=0.25)
+    assert np.array_equal(host.pfm_read(f), a[1:] * np.float32(0.25))
+    open(f, "wb").write(b"P6\n5 7\n255\n")
+    with pytest.raises(Exception):
+        host.pfm_read(f)
+
+
 def test_checkpoint_round_trip(tmp_path):
     rng = np.random.default_rng(3)
     a = rng.random((7, 11, 3), dtype=np.float32) * 100
