@@ -413,7 +413,7 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
       const int L = (int)leaves.size();
       std::vector<Box> lb((size_t)L), suf((size_t)L);
       for (int k = 0; k < L; k++) lb[k] = box_of(leaves[k]);
-      const int exact_len = L <= (1 << 16) ? L : 64;
+      const int exact_len = 4096;   // (sweeping only runs of <= 64 leaves position by position: 0.3 s less per 5.9 M-leaf scene, 5 % slower frames)
       struct Job { int a, b; double anc_sa; int close; };     // close >= 0: "subtree of emitted node `close` ends here"
       std::vector<Job> st;
       st.push_back({0, L, -1.0, -1});
@@ -422,8 +422,8 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
         const Job j = st.back(); st.pop_back();
         if (j.close >= 0) { x2nodes[j.close].hi.z = i2f((int32_t)x2nodes.size()); continue; }
         if (j.b - j.a == 1) { x2nodes.push_back(nodes[leaves[j.a]]); top = false; continue; }
-        // the sweep: every position of the run; in trees of millions of leaves only runs of up to 64 leaves are swept
-        // position by position, longer ones at up to 128 evenly spaced positions (4x cheaper per leaf and level)
+        // the sweep: every position of a run of up to 4096 leaves; of a longer run (trees of millions of leaves) 128 evenly
+        // spaced positions
         const int len = j.b - j.a;
         double best = std::numeric_limits<double>::infinity();
         int cut = j.a + 1;

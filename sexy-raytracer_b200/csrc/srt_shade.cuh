@@ -3,7 +3,8 @@
 // material.h, pbr.h, camera.h:40-50.  Compiled with -fmad=false (see srt_core.cuh).
 #pragma once
 #ifndef SRT_SMALL_CODE
-#define SRT_SMALL_CODE 0   /* A/B builds: 1 = sinf and philox as out-of-line functions (one copy each in the shade kernels' instruction stream) */
+#define SRT_SMALL_CODE 1   /* sinf and philox as out-of-line functions: one copy each in the shade kernels' instruction stream (4.1 k -> 3.2 k
+                              instructions, k_wf_shade2c 0.431 -> 0.412 ms per wave on B200); 0 = inlined everywhere */
 #endif
 #include "srt_core.cuh"
 #include "../../include/srt.h"
