@@ -15,7 +15,13 @@ namespace srt {
 __device__ __noinline__ float sinf_once(float v) { return sinf(v); }
 #define SRT_SINF sinf_once
 #define SRT_PHILOX_INLINE __device__ __noinline__
+#if SRT_SMALL_CODE >= 2
+#define SRT_TEXVAL_INLINE __device__ __noinline__
 #else
+#define SRT_TEXVAL_INLINE __device__ __forceinline__
+#endif
+#else
+#define SRT_TEXVAL_INLINE __device__ __forceinline__
 #define SRT_SINF sinf
 #define SRT_PHILOX_INLINE __device__ __forceinline__
 #endif
@@ -146,7 +152,7 @@ __device__ __forceinline__ V3 image_value(const Tex& t, float u, float v) {
   return mk((float)px.x, (float)px.y, (float)px.z);
 }
 
-__device__ __forceinline__ V3 texture_value(const Scene& sc, int id, float u, float v, V3 p) {
+SRT_TEXVAL_INLINE V3 texture_value(const Scene& sc, int id, float u, float v, V3 p) {
   const Tex* t = &sc.texs[id];
   int kind = __ldg(&t->kind);
   float scale = 1.0f;
