@@ -127,8 +127,9 @@ inline void srt_rotated_grid(int s, float* x, float* y) {
 }
 
 // One sample of one pixel: the two ray-generation Philox blocks, main.cpp:210-211, camera.h:40-50
+template <bool SMALL = false>
 __device__ __forceinline__ Ray generate_ray(const RenderArgs& A, int x, int y, uint32_t pixel, uint32_t sample) {
-  uint4 a = philox(A.seed, pixel, sample, 0), c = philox(A.seed, pixel, sample, 1);
+  uint4 a = philox_sel<SMALL>(A.seed, pixel, sample, 0), c = philox_sel<SMALL>(A.seed, pixel, sample, 1);
   float ju = u01(a.x), jv = u01(a.y);
   if (A.sampler == 1) { const float2 g = __ldg(A.grid + ((int)sample - A.grid_begin)); ju = g.x; jv = g.y; }   // main.cpp:214-215
   float u = ((float)x + ju) / (float)(A.W - 1);
@@ -141,7 +142,7 @@ __device__ __forceinline__ Ray generate_ray(const RenderArgs& A, int x, int y, u
 // One finished segment of a path: main.cpp:39-51 after world.hit returned (prim, t).  Updates the path's
 // radiance L and throughput thr (rayColor's recursion L = e0 + a0*(e1 + a1*(...)) unrolled), replaces r by
 // the scattered ray and advances bounce.  Returns true when the path ends here.
-template <bool COUNT>
+template <bool COUNT, bool SMALL = false>
 __device__ __forceinline__ bool shade_segment(const Scene& sc, const RenderArgs& A, uint32_t pixel, uint32_t sample, int& bounce,
                                               Ray& r, int prim, float t, V3& L, V3& thr, Counters& cnt) {
   if (prim < 0) {                                                         // miss -> background, main.cpp:39-40
@@ -154,7 +155,7 @@ __device__ __forceinline__ bool shade_segment(const Scene& sc, const RenderArgs&
   const Mat m = sc.mats[mat_id];
   Rec rec;
   finish_hit<true>(sc, prim, r, t, (m.flags & MAT_NEEDS_UV) != 0, (m.flags & MAT_NEEDS_TBN) != 0, rec);
-  const uint4 x4 = philox(A.seed, pixel, sample, 2u + (uint32_t)bounce);
+  const uint4 x4 = philox_sel<SMALL>(A.seed, pixel, sample, 2u + (uint32_t)bounce);
   V3 rvec = mk(0, 0, 0);
   if (m.kind == SRT_MAT_PBR) rvec = sample_unit_vector(u01(x4.x), u01(x4.y));
   else if (m.kind == SRT_MAT_METAL) rvec = sample_unit_ball(u01(x4.x), u01(x4.y), u01(x4.z));

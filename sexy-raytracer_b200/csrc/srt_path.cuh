@@ -98,7 +98,7 @@ __device__ __forceinline__ void path_shade_phase(const Scene& sc, const RenderAr
         int bounce = __float_as_int(t4.w);
         Ray ry; ry.o = mk(o.x, o.y, o.z); ry.time = o.w; ry.d = mk(d.x, d.y, d.z);
         V3 thr = mk(t4.x, t4.y, t4.z), L = mk(0, 0, 0);
-        const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, ry, h.x, __int_as_float(h.y), L, thr, cnt);
+        const bool done = shade_segment<COUNT, true>(sc, A, id.x, id.y, bounce, ry, h.x, __int_as_float(h.y), L, thr, cnt);
         if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) { atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z); }
         if (done) ended = true;
         else {
@@ -138,7 +138,7 @@ __device__ __forceinline__ void path_shade_phase(const Scene& sc, const RenderAr
       const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
       if (x < A.W && y < A.H) {
         const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
-        const Ray ry = generate_ray(A, x, y, pixel, sample);
+        const Ray ry = generate_ray<true>(A, x, y, pixel, sample);
         pool.ray_o[g] = make_float4(ry.o.x, ry.o.y, ry.o.z, ry.time);
         pool.ray_d[g] = make_float4(ry.d.x, ry.d.y, ry.d.z, 0.0f);
         pool.thr[g] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));

@@ -14,7 +14,6 @@ namespace srt {
 #if SRT_SMALL_CODE
 __device__ __noinline__ float sinf_once(float v) { return sinf(v); }
 #define SRT_SINF sinf_once
-#define SRT_PHILOX_INLINE __device__ __noinline__
 #if SRT_SMALL_CODE >= 2
 #define SRT_TEXVAL_INLINE __device__ __noinline__
 #else
@@ -23,7 +22,6 @@ __device__ __noinline__ float sinf_once(float v) { return sinf(v); }
 #else
 #define SRT_TEXVAL_INLINE __device__ __forceinline__
 #define SRT_SINF sinf
-#define SRT_PHILOX_INLINE __device__ __forceinline__
 #endif
 
 struct Rec {
@@ -272,7 +270,7 @@ __device__ __forceinline__ bool material_scatter(const Scene& sc, const Mat& m, 
 }
 
 // ---- random numbers (new: per-(pixel, sample) Philox4x32-10; DESIGN.md "random numbers") --------
-SRT_PHILOX_INLINE uint4 philox(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
+__device__ __forceinline__ uint4 philox(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
   uint32_t c0 = pixel, c1 = sample, c2 = block, c3 = 0;
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll
@@ -283,6 +281,13 @@ SRT_PHILOX_INLINE uint4 philox(uint64_t seed, uint32_t pixel, uint32_t sample, u
     k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
   }
   return make_uint4(c0, c1, c2, c3);
+}
+// one out-of-line copy for the wavefront's shade kernels (three call sites: the kernel is bound by its instruction cache,
+// not by this call); the megakernels keep the inlined form (config 2: 7 % faster that way)
+__device__ __noinline__ uint4 philox_ool(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) { return philox(seed, pixel, sample, block); }
+template <bool SMALL>
+__device__ __forceinline__ uint4 philox_sel(uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
+  return (SMALL && SRT_SMALL_CODE) ? philox_ool(seed, pixel, sample, block) : philox(seed, pixel, sample, block);
 }
 __device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 

@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
         pixel = id.x; sample = id.y;
         r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
         thr = mk(t4.x, t4.y, t4.z); L = mk(0, 0, 0);
-        const bool done = shade_segment<COUNT>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
+        const bool done = shade_segment<COUNT, true>(sc, A, pixel, sample, bounce, r, h.x, __int_as_float(h.y), L, thr, cnt);
         if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                           // this segment's term (NaN included)
           float* px = accum + (size_t)pixel * 3;
           atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);     // result unused -> red.global.add.f32
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade(Scene sc
         if (x < A.W && y < A.H) {
           pixel = (uint32_t)(y * A.W + x);
           sample = (uint32_t)(A.sample_begin + s_off);
-          r = generate_ray(A, x, y, pixel, sample);
+          r = generate_ray<true>(A, x, y, pixel, sample);
           L = mk(0, 0, 0); thr = mk(1, 1, 1); bounce = 0;
           new_path = wrote_ray = true;
         }
@@ -465,7 +465,7 @@ __global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shad
       int bounce = __float_as_int(th4.w);
       Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
       V3 thr = mk(th4.x, th4.y, th4.z), L = mk(0, 0, 0);
-      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
+      const bool done = shade_segment<COUNT, true>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
       if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                      // this segment's emitted term (NaN included)
         float* px = accum + (size_t)id.x * 3;
         atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
@@ -498,7 +498,7 @@ __global__ void __launch_bounds__(TS, SRT_SHADE_MIN_BLOCKS * 256 / TS) k_wf_shad
         const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
         if (x < A.W && y < A.H) {
           const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
-          const Ray r = generate_ray(A, x, y, pixel, sample);
+          const Ray r = generate_ray<true>(A, x, y, pixel, sample);
           pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
           pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
           pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2c(Scene 
       int bounce = __float_as_int(th4.w);
       Ray r; r.o = mk(o.x, o.y, o.z); r.time = o.w; r.d = mk(d.x, d.y, d.z);
       V3 thr = mk(th4.x, th4.y, th4.z), L = mk(0, 0, 0);
-      const bool done = shade_segment<COUNT>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
+      const bool done = shade_segment<COUNT, true>(sc, A, id.x, id.y, bounce, r, hh.x, __int_as_float(hh.y), L, thr, cnt);
       if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {                      // this segment's emitted term (NaN included)
         float* px = accum + (size_t)id.x * 3;
         atomicAdd(px, L.x); atomicAdd(px + 1, L.y); atomicAdd(px + 2, L.z);
@@ -649,7 +649,7 @@ __global__ void __launch_bounds__(256, SRT_SHADE_MIN_BLOCKS) k_wf_shade2c(Scene 
         const int x = (tile % A.tiles_x) * 8 + (l & 7), y = (tile / A.tiles_x) * 4 + (l >> 3);
         if (x < A.W && y < A.H) {
           const uint32_t pixel = (uint32_t)(y * A.W + x), sample = (uint32_t)(A.sample_begin + s_off);
-          const Ray r = generate_ray(A, x, y, pixel, sample);
+          const Ray r = generate_ray<true>(A, x, y, pixel, sample);
           pool.ray_o[k] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
           pool.ray_d[k] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(1));
           pool.thr[k] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(0));
