@@ -54,7 +54,7 @@ path_fn pick_path(bool count, int fmt) {
   return fmt == 16 ? k_wf_path<false, 16, THREADS> : k_wf_path<false, 32, THREADS>;
 }
 #ifndef SRT_WF_SLOTS_SMEM
-#define SRT_WF_SLOTS_SMEM (1 << 24)
+#define SRT_WF_SLOTS_SMEM (1 << 25)
 #endif
 #ifndef SRT_SHADE_DEFAULT
 #define SRT_SHADE_DEFAULT 3       /* 2: k_wf_shade2, 3: k_wf_shade2c (carried remainders; -7 % per wave, B200) */
@@ -98,9 +98,9 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   cudaError_t e;
   plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
   // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
-  // Pool: 8 Mi slots (537 MB); 16 Mi when the tree is walked from shared memory - a wave of k_wf_extend2 is then only ~1 ms, and
+  // Pool: 8 Mi slots (537 MB); 32 Mi (2.1 GB) when the tree is walked from shared memory - a wave of k_wf_extend2 is then only ~1 ms, and
   // the fixed cost of a wave (two launches, node staging, the drain at its end) is worth halving: config 4, 5000 spp:
-  // 8 / 12 / 16 Mi slots -> 5 051 / 5 289 / 5 413 M segments/s (B200).
+  // 8 / 12 / 16 / 24 / 32 Mi slots -> 5 051 / 5 289 / 5 413 / 5 558 / 5 630 M segments/s (B200).
   plan.wf_slots = s->nodes_in_smem ? SRT_WF_SLOTS_SMEM : 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
   // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
   // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, round-1 sweep recorded in profiles/r1_c5_extend_summary.md); below 1024 the rate falls linearly
