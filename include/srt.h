@@ -225,6 +225,25 @@ srt_status  srt_trace_rays(srt_scene* scene, const srt_ray* rays, int64_t n, flo
  * ray ordering it uses for this scene - one wave over n pool slots; returns the primitive id (-1 = miss) and t bits per ray  */
 srt_status  srt_trace_rays_wavefront(srt_scene* scene, const srt_ray* rays, int64_t n, int32_t* out_prim, float* out_t);
 
+/* ---- the same wave for callers that may not allocate -------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code
+ * under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same kernels, launch shape and results as
+ * srt_trace_rays_wavefront, but:
+ *   - rays_dev, out_prim_dev and out_t_dev are DEVICE pointers on the scene's GPU (n srt_ray in, n int32 + n float out); the call
+ *     makes no host copy and calls no cudaMalloc / cudaFree / allocating library routine: its scratch (ray slots, hit records,
+ *     cursors) is a static device array of SRT_STATIC_MAX_RAYS * 40 + 256 bytes (2.5 MiB) that every GPU which loads the library
+ *     holds until the process exits;
+ *   - n > SRT_STATIC_MAX_RAYS returns SRT_ERR_UNSUPPORTED (split the batch, or use srt_trace_rays_wavefront);
+ *   - every call on a GPU shares that array (it keeps the last call's contents; what must start at zero is cleared by the call):
+ *     calls that overlap on one GPU race - one call at a time per GPU;
+ *   - rays are never re-ordered before the wave (trees beyond the L2 sort them in srt_trace_rays_wavefront); results do not
+ *     depend on the order.
+ * The call returns after the scene's device stream has been synchronised.                                                      */
+#define SRT_STATIC_MAX_RAYS 65536
+int64_t     srt_static_max_rays(void);
+srt_status  srt_trace_rays_wavefront_static(srt_scene* scene, const srt_ray* rays_dev, int64_t n, int32_t* out_prim_dev,
+                                            float* out_t_dev);
+
 /* ---- one frame: replaces glDevice::rtFrame + the loop main.cpp:200-227 ------------------------
  * out_sum_rgb  (optional) [H*W*3] float: sum over this call's samples of rayColor, row 0 = top
  * out_rgba8    (optional) [H*W*4] writeColorTarget output (color.h:25-41), only meaningful when this

@@ -98,6 +98,8 @@ PROTOTYPES = {
     "srt_scene_device_bytes": (C.c_int64, [_vp]),
     "srt_trace_rays": (C.c_int, [_vp, _vp, C.c_int64, C.c_float, C.c_float, _vp]),
     "srt_trace_rays_wavefront": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp]),
+    "srt_trace_rays_wavefront_static": (C.c_int, [_vp, _vp, C.c_int64, _vp, _vp]),
+    "srt_static_max_rays": (C.c_int64, []),
     "srt_aabb_kat": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int32, _vp, _vp]),
     "srt_render": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp, C.POINTER(Stats)]),
     "srt_render_accumulate": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, C.POINTER(Stats)]),

@@ -31,6 +31,14 @@ static srt_status fail(srt_status s, const std::string& msg) { g_err = msg; retu
     }                                                                                              \
   } while (0)
 
+// ---- scratch of srt_trace_rays_wavefront_static (srt_noalloc.cuh): an entry point that allocates nothing ---------------------
+// A file-scope device array: every GPU that loads this library holds SRT_STATIC_SCRATCH_BYTES (2.5 MiB + 256 B) until the process
+// exits.  Layout: WfCursors (256 bytes reserved) | ray_o[MAX] float4 | ray_d[MAX] float4 | hit[MAX] int2.
+// In HOST code this name is only a stand-in for the symbol, not a device address: srt_device_create asks the runtime for the address
+// on each device (cudaGetSymbolAddress with that device current) and keeps it in srt_device::static_scratch.
+#define SRT_STATIC_SCRATCH_BYTES (256 + (size_t)SRT_STATIC_MAX_RAYS * (16 + 16 + 8))
+static __device__ __align__(256) unsigned char g_static_scratch[SRT_STATIC_SCRATCH_BYTES];
+
 struct srt_device {
   int gpu = 0;
   int sm_count = 0;
@@ -53,6 +61,8 @@ struct srt_device {
   unsigned* d_sort = nullptr; size_t sort_cap = 0;  // ray ordering (k_wf_keys): keys in/out, slots in/out, 4 x sort_cap words
   void* d_sort_tmp = nullptr; size_t sort_tmp_bytes = 0;
   void* d_path = nullptr; size_t path_capacity = 0;  // k_wf_path's warp-private path slots (srt_path.cuh)
+  void* static_scratch = nullptr;                  // device address of g_static_scratch on THIS gpu (nullptr: see static_scratch_err)
+  std::string static_scratch_err;
   int async_alloc = 0;                             // scene arenas through cudaMallocAsync / cudaFreeAsync on `stream`
   void* h_stage = nullptr; size_t h_stage_cap = 0;  // pinned staging of srt_scene_create's arena (scenes up to SCENE_STAGE_MAX bytes)
 };
@@ -112,6 +122,13 @@ srt_status srt_device_create(int gpu_id, srt_device** out) try {
       if (cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep) == cudaSuccess) d->async_alloc = 1;
     }
     cudaGetLastError();
+  }
+  {  // the address of the static scratch array on this device (this device is current); a failure only disables
+     // srt_trace_rays_wavefront_static, which then reports it
+    void* p = nullptr;
+    const cudaError_t es = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (es == cudaSuccess && p) d->static_scratch = p;
+    else { d->static_scratch_err = std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(es); cudaGetLastError(); }
   }
   *out = d;
   return SRT_OK;
@@ -687,3 +704,4 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
 
 #include "srt_launch.cuh"
 #include "srt_group.cuh"
+#include "srt_noalloc.cuh"

@@ -129,6 +129,11 @@ class DeviceScene:
         _check(lib().srt_trace_rays_wavefront(self.h, _ptr(rays), len(rays), _ptr(prim), _ptr(t)))
         return prim, t
 
+    def trace_wavefront_static(self, rays_dev_ptr, n, out_prim_dev_ptr, out_t_dev_ptr):
+        """srt_trace_rays_wavefront_static: the same wave on DEVICE pointers (ints / void*), allocating nothing; the caller owns
+        the three device buffers.  At most srt_static_max_rays() rays per call; one call at a time per GPU."""
+        _check(lib().srt_trace_rays_wavefront_static(self.h, rays_dev_ptr, n, out_prim_dev_ptr, out_t_dev_ptr))
+
     def render(self, params=None, want_sum=True, want_rgba=True, camera=None):
         """srt_render with host buffers -> (sum [H,W,3] f32 | None, rgba [H,W,4] u8 | None, Stats)"""
         P = params if params is not None else self.scene.render_params()
