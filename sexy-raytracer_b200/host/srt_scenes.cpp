@@ -57,7 +57,41 @@ bool referenceScene(int which, const std::string& dataDir, srt_host_scene& S, st
   const std::string savedDir = gltfConfig().textureDir;
   gltfConfig().textureDir = dataDir;                    // stands for the literal "../data/" of model.h:393
   randomReset();                                        // the generator's state at the start of main()
-  if (which == 1) {
+  if (which == 11 || which == 12) {
+    // NOT in the reference's main.cpp: config 1's spheres with bvhNodes nested inside the outer bvhNode's list, which bvh.h:14
+    // allows (any hittable).  11: the small spheres form their own tree next to the ground and the three large spheres;
+    // 12: as 11, and the outer list holds nothing but one bvhNode over all of that (a span of one object, bvh.h:67-69).
+    // The spheres are created first, with config 1's draws, so their parameters equal config 1's.
+    hittableList field, top;
+    auto checkerTex = make_shared<checker>(color3f(0.2f, 0.3f, 0.1f), color3f(0.9f, 0.9f, 0.9f));
+    top.add(make_shared<sphere>(vec3f(0, -1000, 0.0f), vec3f(0, -1000, 0.0f), 0, 1.0f, 1000, make_shared<pbrMetallicRoughness>(checkerTex)));
+    for (int a = -11; a < 11; a++) {
+      for (int b = -11; b < 11; b++) {
+        auto choose_mat = randomFloat();
+        vec3f center(a + 0.9 * randomFloat(), 0.2f, b + 0.9f * randomFloat());
+        if (length(center - vec3f(4, 0.2, 0)) > 0.9) {
+          if (choose_mat < 0.8) {
+            color3f albedo(randomFloat() * randomFloat(), randomFloat() * randomFloat(), randomFloat() * randomFloat());
+            auto sphere_material = diffuse255(albedo);
+            vec3f center2 = center + vec3f(0, randomFloat(0, 0.5f), 0);
+            field.add(make_shared<sphere>(center, center2, 0, 1.0f, 0.2f, sphere_material));
+          } else if (choose_mat < 0.95f) {
+            auto albedo = randomVec3f(0.5f, 1);
+            auto fuzz = randomFloat(0, 0.5f);
+            field.add(make_shared<sphere>(center, center, 0, 1.0f, 0.2f, make_shared<metal>(albedo, fuzz)));
+          } else {
+            field.add(make_shared<sphere>(center, center, 0, 1.0f, 0.2f, make_shared<dielectric>(1.5f)));
+          }
+        }
+      }
+    }
+    top.add(make_shared<bvhNode>(field, 0, 1));
+    top.add(make_shared<sphere>(vec3f(0, 1, 0), vec3f(0, 1, 0), 0, 1.0f, 1.0f, make_shared<dielectric>(1.5)));
+    top.add(make_shared<sphere>(vec3f(-4, 1, 0), vec3f(-4, 1, 0), 0, 1.0f, 1.0f, diffuse255(color3f(0.4f, 0.2f, 0.1f))));
+    top.add(make_shared<sphere>(vec3f(4.0f, 1.0f, 0), vec3f(4.0f, 1.0f, 0), 0, 1.0f, 1.0f, make_shared<metal>(color3f(0.7, 0.6, 0.5), 0.0)));
+    if (which == 11) objects = top;
+    else objects.add(make_shared<bvhNode>(top, 0, 1));
+  } else if (which == 1) {
     auto checkerTex = make_shared<checker>(color3f(0.2f, 0.3f, 0.1f), color3f(0.9f, 0.9f, 0.9f));
     objects.add(make_shared<sphere>(vec3f(0, -1000, 0.0f), vec3f(0, -1000, 0.0f), 0, 1.0f, 1000, make_shared<pbrMetallicRoughness>(checkerTex)));
     for (int a = -11; a < 11; a++) {                    // main.cpp:92-122

@@ -107,6 +107,13 @@ struct Soa {
     }
     tris.push_back(t);
   }
+  // a box as a pseudo triangle (v0 = v2 = min corner, v1 = max corner): triangle::boundingBox of it is the box itself, so the
+  // builder sorts and unions a nested bvhNode exactly like the reference does through bvhNode::boundingBox (bvh.h:107-110)
+  void add_box(const float* bmin, const float* bmax) {
+    v0.insert(v0.end(), bmin, bmin + 3); v1.insert(v1.end(), bmax, bmax + 3); v2.insert(v2.end(), bmin, bmin + 3);
+    for (auto* U : {&uv0, &uv1, &uv2}) U->insert(U->end(), 2, 0.0f);
+    tris.push_back(nullptr);
+  }
   void add(const sphere* s) {
     c0.insert(c0.end(), s->center0.d, s->center0.d + 3);
     c1.insert(c1.end(), s->center1.d, s->center1.d + 3);
@@ -155,13 +162,52 @@ bool collect(const std::vector<shared_ptr<hittable>>& objs, size_t start, size_t
 bvhNode::bvhNode(const std::vector<shared_ptr<hittable>>& srcObjects, size_t start, size_t end, float t0, float t1)
     : time0(t0), time1(t1) {
   if (start > end || end > srcObjects.size()) { error = "bad span"; return; }
+  // The span may hold spheres, triangles and other bvhNodes (bvh.h:14: any hittable).  A nested bvhNode takes part in this
+  // tree's construction through its root box only - exactly what the reference's comparator and surroundingBox see - and its
+  // own nodes are spliced in afterwards where the builder put the box.
+  std::vector<const bvhNode*> nested;
+  bool plain = true;
+  for (size_t i = start; i < end; i++)
+    if (auto nb = dynamic_cast<const bvhNode*>(srcObjects[i].get())) {
+      if (!nb->error.empty()) { error = "nested bvhNode: " + nb->error; return; }
+      if (nb->nodes.empty()) { error = "nested bvhNode without nodes"; return; }
+      plain = false;
+    }
   Soa soa;
   std::vector<int32_t> order;
   std::vector<std::shared_ptr<mesh>> keep;
-  if (!collect(srcObjects, start, end, soa, order, keep, error)) return;
-  // prims in ID order (triangles, then spheres)
-  prims.resize(end - start);
-  for (size_t i = start; i < end; i++) prims[order[i - start]] = srcObjects[i];
+  if (plain) {
+    if (!collect(srcObjects, start, end, soa, order, keep, error)) return;
+    // prims in ID order (triangles, then spheres)
+    prims.resize(end - start);
+    for (size_t i = start; i < end; i++) prims[order[i - start]] = srcObjects[i];
+  } else {
+    // builder ids: triangles and nested boxes share the triangle numbering (span order), spheres follow
+    size_t n_tb = 0;
+    for (size_t i = start; i < end; i++) if (!dynamic_cast<const sphere*>(srcObjects[i].get())) ++n_tb;
+    order.resize(end - start);
+    size_t ti = 0, si = 0;
+    for (size_t i = start; i < end; i++) {
+      const hittable* h = srcObjects[i].get();
+      if (auto t = dynamic_cast<const triangle*>(h)) {
+        auto m = t->parentMesh.lock();
+        if (!m) { error = "triangle whose mesh is gone"; return; }
+        if (t->vertices[0] >= m->positions.size() || t->vertices[1] >= m->positions.size() || t->vertices[2] >= m->positions.size()) {
+          error = "triangle index beyond its mesh's positions"; return;
+        }
+        keep.push_back(m);
+        soa.add(t, m.get());
+        order[i - start] = (int32_t)ti++;
+      } else if (auto nb = dynamic_cast<const bvhNode*>(h)) {
+        soa.add_box(nb->nodes[0].bmin, nb->nodes[0].bmax);
+        order[i - start] = (int32_t)ti++;
+      } else if (dynamic_cast<const sphere*>(h)) {
+        continue;
+      } else { error = "bvhNode over an object that is neither a sphere, a triangle nor a bvhNode"; return; }
+    }
+    for (size_t i = start; i < end; i++)
+      if (auto sp = dynamic_cast<const sphere*>(srcObjects[i].get())) { soa.add(sp); order[i - start] = (int32_t)(n_tb + si++); }
+  }
   srt_bvh_node* out = nullptr;
   int64_t n = 0;
   uint64_t draws = 0;
@@ -174,6 +220,78 @@ bvhNode::bvhNode(const std::vector<shared_ptr<hittable>>& srcObjects, size_t sta
   Rng& r = rng();                       // the constructor's randomInt(0,2) calls, one per node (bvh.h:60)
   r.gen.discard(draws);
   r.draws += draws;
+  if (plain) return;
+
+  // ---- splice: final primitive ids (triangles of this span, then the nested trees' triangles, then spheres likewise) and nodes
+  std::vector<shared_ptr<hittable>> tri_objs, sph_objs;
+  std::vector<int32_t> tri_final(soa.tris.size(), -1);      // builder triangle id -> final id, or -1 - k for nested tree k
+  {
+    size_t b = 0;
+    for (size_t i = start; i < end; i++) {
+      const hittable* h = srcObjects[i].get();
+      if (dynamic_cast<const triangle*>(h)) { tri_final[b++] = (int32_t)tri_objs.size(); tri_objs.push_back(srcObjects[i]); }
+      else if (auto nb = dynamic_cast<const bvhNode*>(h)) { tri_final[b++] = -1 - (int32_t)nested.size(); nested.push_back(nb); }
+    }
+    for (size_t i = start; i < end; i++) if (dynamic_cast<const sphere*>(srcObjects[i].get())) sph_objs.push_back(srcObjects[i]);
+  }
+  std::vector<size_t> ntri(nested.size()), tri_base(nested.size()), sph_base(nested.size());
+  for (size_t k = 0; k < nested.size(); k++) {
+    size_t c = 0;
+    for (auto& o : nested[k]->prims) if (dynamic_cast<const triangle*>(o.get())) ++c;      // (prims are triangles first)
+    ntri[k] = c;
+    tri_base[k] = tri_objs.size();
+    tri_objs.insert(tri_objs.end(), nested[k]->prims.begin(), nested[k]->prims.begin() + c);
+  }
+  const size_t n_tri_total = tri_objs.size();
+  for (size_t k = 0; k < nested.size(); k++) {
+    sph_base[k] = sph_objs.size();
+    sph_objs.insert(sph_objs.end(), nested[k]->prims.begin() + ntri[k], nested[k]->prims.end());
+  }
+  prims = tri_objs;
+  prims.insert(prims.end(), sph_objs.begin(), sph_objs.end());
+  const size_t n_tb_builder = soa.tris.size();
+  auto final_leaf = [&](int32_t builder_id, int32_t& nested_k) -> int32_t {       // -> final primitive id, or nested_k >= 0
+    nested_k = -1;
+    if ((size_t)builder_id < n_tb_builder) {
+      const int32_t f = tri_final[builder_id];
+      if (f < 0) { nested_k = -1 - f; return -1; }
+      return f;
+    }
+    return (int32_t)(n_tri_total + ((size_t)builder_id - n_tb_builder));          // this span's spheres come first among the spheres
+  };
+  auto append_nested = [&](size_t k) -> int32_t {                                  // copies tree k behind `nodes`, returns its root
+    const int32_t off = (int32_t)nodes.size();
+    for (const srt_bvh_node& src : nested[k]->nodes) {
+      srt_bvh_node nd = src;
+      for (int32_t* c : {&nd.left, &nd.right}) {
+        if (*c == SRT_BVH_NONE) continue;
+        if (*c >= 0) *c += off;
+        else {
+          const size_t id = (size_t)(~*c);
+          const size_t f = id < ntri[k] ? tri_base[k] + id : n_tri_total + sph_base[k] + (id - ntri[k]);
+          *c = ~(int32_t)f;
+        }
+      }
+      nodes.push_back(nd);
+    }
+    return off;
+  };
+  const size_t n_outer = nodes.size();
+  for (size_t i = 0; i < n_outer; i++) {
+    int32_t kl = -1, kr = -1;
+    const bool single = nodes[i].right == SRT_BVH_NONE;       // a span of one object: the reference sets left = right (bvh.h:67-69)
+    if (nodes[i].left < 0) {
+      const int32_t f = final_leaf(~nodes[i].left, kl);
+      if (kl < 0) nodes[i].left = ~f;
+    }
+    if (!single && nodes[i].right < 0) {
+      const int32_t f = final_leaf(~nodes[i].right, kr);
+      if (kr < 0) nodes[i].right = ~f;
+    }
+    if (kl >= 0) { const int32_t root = append_nested((size_t)kl); nodes[i].left = root; }
+    if (single && kl >= 0) { const int32_t root = append_nested((size_t)kl); nodes[i].right = root; }   // hit twice, as the reference does
+    if (kr >= 0) { const int32_t root = append_nested((size_t)kr); nodes[i].right = root; }
+  }
 }
 
 // ---- flattening ------------------------------------------------------------------------------------------------------

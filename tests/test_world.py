@@ -500,3 +500,85 @@ def test_gltf_rejects_malformed_accessors(tmp_path):
             s = load(doc(**over), quirks)
             assert s is None or s.n_tri <= 1, over      # either refused, or (a field the reference's rules ignore) loaded in bounds
         assert load(doc(**over), False) is None, over
+
+
+# ---- bvhNode objects nested in another bvhNode's list (bvh.h:14 allows any hittable there) -----------------------------------
+def _nested_map(n_small):
+    """primitive id of scene 11 / 12 -> id of config 1: [ground, big1..3 | small...] -> [ground, small..., big1..3]"""
+    m = np.empty(n_small + 4, np.int64)
+    m[0] = 0
+    m[1:4] = n_small + 1 + np.arange(3)
+    m[4:] = 1 + np.arange(n_small)
+    return m
+
+
+def _nested_rays(scenes, port):
+    import rayset
+    s1 = scenes["c1_shirley"]
+    h = port.from_scene(s1)
+    try:
+        pin = rayset.pinhole(s1, step=2)
+        want = port.trace(h, pin)
+        rays = np.concatenate([pin, rayset.secondary(want, 20000, 3), rayset.random_rays(10000, 4)])
+        return rays, port.trace(h, rays)
+    finally:
+        port.free(h)
+
+
+@pytest.mark.parametrize("which", [11, 12])
+def test_nested_bvh_nodes_flatten_to_the_same_hits(which, scenes, port, tmp_path):
+    """Scenes 11 / 12 = config 1's spheres (same draws, same parameters) with the small spheres in a bvhNode of their own inside
+    the outer bvhNode's list (12: the outer list holds one bvhNode only - a span of one, hit twice as bvh.h:67-69 does).  The
+    flattening splices the nested tree in where the builder put its root box; a scene of spheres returns the nearest hit whatever
+    the tree (sphere::hit honours tMax), so the hits must be config 1's, primitive for primitive."""
+    s, draws = host.reference_scene(which, str(tmp_path))
+    s1 = scenes["c1_shirley"]
+    n_small = len(s1.sph_r) - 4
+    assert len(s.sph_r) == len(s1.sph_r) and s.n_tri == 0
+    m = _nested_map(n_small)
+    assert np.array_equal(s.sph_c0[np.argsort(m)], s1.sph_c0) and np.array_equal(s.sph_r[np.argsort(m)], s1.sph_r)
+    # a tree: every node reachable once, leaves cover every sphere (12: the nested copy is traversed twice -> twice)
+    left, right = s.nodes["left"], s.nodes["right"]
+    leaves = np.concatenate([~left[left < 0], ~right[(right < 0) & (right != np.iinfo(np.int32).min)]])
+    cnt = np.bincount(leaves, minlength=len(s.sph_r))
+    assert (cnt == (1 if which == 11 else 2)).all()
+    rays, want = _nested_rays(scenes, port)
+    h = port.from_scene(s)
+    try:
+        got = port.trace(h, rays)
+    finally:
+        port.free(h)
+    hit = want["prim"] >= 0
+    assert ((got["prim"] >= 0) == hit).all()
+    assert (m[got["prim"][hit]] == want["prim"][hit]).all()
+    assert (got["t"][hit].view(np.uint32) == want["t"][hit].view(np.uint32)).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", [11, 12])
+def test_nested_bvh_nodes_on_the_gpu(which, device, scenes, port, tmp_path):
+    """the same scenes on the device: srt_trace_rays, the wavefront's extend kernel and a frame against the port"""
+    s, _ = host.reference_scene(which, str(tmp_path))
+    rays, _ = _nested_rays(scenes, port)
+    h = port.from_scene(s)
+    ds = device.upload(s)
+    try:
+        want = port.trace(h, rays)
+        got = ds.trace(rays)
+        assert (got["prim"] == want["prim"]).all()
+        prim, t = ds.trace_wavefront(rays)
+        assert (prim == want["prim"]).all()
+        hit = want["prim"] >= 0
+        assert (t[hit].view(np.uint32) == want["t"][hit].view(np.uint32)).all()
+        s1 = scenes["c1_shirley"]
+        kw = dict(width=160, height=90, spp=8, max_bounce=6, seed=3)
+        P = s1.render_params(**kw)
+        cam = s1.camera_struct()
+        a, _, sa = ds.render(P, camera=cam, want_rgba=False)
+        b, _, sb = ds.render(s1.render_params(variant=2, **kw), camera=cam, want_rgba=False)
+        assert sa.paths == sb.paths == 160 * 90 * 8 and sa.segments == sb.segments
+        fin = np.isfinite(a).all(axis=2)
+        assert np.abs(a[fin] - b[fin]).max() <= 2e-5 * max(1.0, float(np.abs(a[fin]).max()))
+    finally:
+        ds.close()
+        port.free(h)
