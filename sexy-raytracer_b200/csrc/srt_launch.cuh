@@ -98,10 +98,17 @@ static cudaError_t plan_wavefront(srt_scene* s, long long total, RenderPlan& pla
   cudaError_t e;
   plan.smem = s->nodes_in_smem ? s->node_bytes : 0;
   // SRT_WF="slots,threads,th_walk" (tuning sweeps only)
-  // Pool: 8 Mi slots (537 MB); 32 Mi (2.1 GB) when the tree is walked from shared memory - a wave of k_wf_extend2 is then only ~1 ms, and
-  // the fixed cost of a wave (two launches, node staging, the drain at its end) is worth halving: config 4, 5000 spp:
-  // 8 / 12 / 16 / 24 / 32 Mi slots -> 5 051 / 5 289 / 5 413 / 5 558 / 5 630 M segments/s (B200).
-  plan.wf_slots = s->nodes_in_smem ? SRT_WF_SLOTS_SMEM : 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
+  // Pool: 8 Mi slots (537 MB).  When the tree is walked from shared memory a wave of k_wf_extend2 is only ~1 ms per 8 Mi rays, and
+  // the fixed cost of a wave (two launches, node staging, the drain at its end) is worth amortising over more slots - as long as
+  // the frame still refills the pool several times, because the last refill runs with a pool that empties: slots = paths / 8,
+  // between 8 Mi and 32 Mi (2.1 GB).  Measured on B200, M segments/s: config 4 (4.6 G paths) 8 / 12 / 16 / 24 / 32 Mi slots ->
+  // 5 051 / 5 289 / 5 413 / 5 558 / 5 630; a 200-spp 720p frame (184 M paths) 8 / 16 / 32 Mi -> 4 812 / 4 975 / 4 842; config 3
+  // (102 M paths) 8 / 16 / 32 Mi -> 4 662 / 4 705 / 4 436, and on two GPUs (51 M paths each) 8 / 32 Mi -> 8 611 / 6 860.
+  plan.wf_slots = 1 << 23; plan.threads = 1024; plan.wf_th_walk = 16;
+  if (s->nodes_in_smem) {
+    const long long want = total / 8;
+    plan.wf_slots = (int)std::min<long long>(std::max<long long>(want, 1ll << 23), (long long)SRT_WF_SLOTS_SMEM) / 256 * 256;
+  }
   // trees beyond the L2 (sorted rays, srt_wavefront.cuh: k_wf_keys): 2 x 768 threads per SM at 40 registers measured +4 %
   // over 1 x 1024 at 56 (61.2 vs 58.8 M segments/s, round-1 sweep recorded in profiles/r1_c5_extend_summary.md); below 1024 the rate falls linearly
   // ... and a pool of 64 Mi slots (5.4 GB + 1 GB of sort buffers): the more rays one sort orders, the smaller the region of
