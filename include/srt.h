@@ -134,6 +134,14 @@ typedef struct srt_scene_desc {
   const float*   tri_n0;
   const float*   tri_n1;
   const float*   tri_n2;
+  /* optional per-vertex tangents (glTF TANGENT: xyz + handedness w = +-1), [n_tri*4] each, all three or none (NULL = the
+     reference's per-face basis from the UV deltas, calcTangentBasis, model.h:214-235: glTF TANGENT is never read, model.h:335-365).
+     When given, a triangle whose vertices carry a non-zero w is shaded with tangent = unit(r0 t0 + r1 t1 + r2 t2) (the weights of
+     model.h:158-166) and bitangent = w0 * unit(shading normal x tangent); triangles whose three w are 0, and hits where that
+     basis is not finite, keep the per-face basis.  NOT the reference's behaviour. */
+  const float*   tri_tan0;
+  const float*   tri_tan1;
+  const float*   tri_tan2;
 } srt_scene_desc;
 
 /* camera: the ten derived members of camera.h:52-62 (private there; the host class exposes them) */

@@ -86,10 +86,11 @@ srt_status srt_checkpoint_read2(const char* path, int32_t* width, int32_t* heigh
 typedef struct srt_host_scene srt_host_scene;
 srt_status srt_host_scene_reference(int which, const char* data_dir, srt_host_scene** out);
 /* options: bit 0 = gltfOptions::referenceQuirks (1 = load exactly like model.h:301-460), bit 1 = smoothNormals,
- * bit 2 = sampleMetallicRoughness (include/srt_world.hpp; the last two are NOT reference behaviour) */
+ * bit 2 = sampleMetallicRoughness, bit 3 = vertexTangents (include/srt_world.hpp; the last three are NOT reference behaviour) */
 #define SRT_GLTF_REFERENCE_QUIRKS 1
 #define SRT_GLTF_SMOOTH_NORMALS 2
 #define SRT_GLTF_SAMPLE_MR 4
+#define SRT_GLTF_VERTEX_TANGENTS 8
 srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, int options, srt_host_scene** out);
 const srt_scene_desc* srt_host_scene_desc(const srt_host_scene* s);
 uint64_t   srt_host_scene_draws(const srt_host_scene* s);      /* generator outputs consumed by the set-up */

@@ -212,6 +212,7 @@ class mesh : public hittable {          // model.h:52-76
   std::vector<vec3f> positions;
   std::vector<vec2f> texcoords;
   std::vector<vec3f> normals;           // glTF NORMAL, filled only under gltfOptions::smoothNormals (the reference never reads it)
+  std::vector<vec4f> tangents;          // glTF TANGENT (xyz + handedness), filled only under gltfOptions::vertexTangents
   shared_ptr<material> matPtr;
  private:
   mesh() = default;
@@ -238,6 +239,8 @@ struct gltfOptions {
   // Two things the reference does not do at all, both off by default and independent of referenceQuirks:
   bool smoothNormals = false;           // read NORMAL into mesh::normals; a scene holding any is shaded with interpolated
                                         // vertex normals (srt_scene_desc::tri_n0..2); meshes without NORMAL keep face normals
+  bool vertexTangents = false;          // read TANGENT into mesh::tangents; triangles of such meshes are shaded with the interpolated
+                                        // tangent (srt_scene_desc::tri_tan0..2) instead of calcTangentBasis' per-face one (model.h:214-235)
   bool sampleMetallicRoughness = false; // materials with a metallicRoughnessTexture sample it (glTF 2.0: metal = B * factor,
                                         // roughness = G * factor) instead of storing it unused (material.h:78)
 };
@@ -283,6 +286,7 @@ class flatScene {
   std::string error;
   std::vector<float> tri_v0, tri_v1, tri_v2, tri_uv0, tri_uv1, tri_uv2, sph_c0, sph_c1, sph_t0, sph_t1, sph_r;
   std::vector<float> tri_n0, tri_n1, tri_n2;         // empty unless some mesh carries vertex normals
+  std::vector<float> tri_tan0, tri_tan1, tri_tan2;   // empty unless some mesh carries vertex tangents (4 floats per triangle vertex)
   std::vector<int32_t> tri_mat, sph_mat;
   std::vector<srt_bvh_node> nodes;
   std::vector<srt_material> materials;

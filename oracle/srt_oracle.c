@@ -62,6 +62,7 @@ typedef struct so_scene {
   int64_t n_tri, n_sph, n_nodes;
   float *v0, *v1, *v2, *uv0, *uv1, *uv2; int32_t* tri_mat;
   float *n0, *n1, *n2;   /* optional per-vertex normals (srt.h: tri_n0), NULL = the reference's flat shading */
+  float *tg0, *tg1, *tg2; /* optional per-vertex tangents xyz + handedness (srt.h: tri_tan0), NULL = the per-face basis */
   float *c0, *c1, *t0, *t1, *r; int32_t* sph_mat;
   srt_bvh_node* nodes;
   int32_t n_mat, n_tex;
@@ -79,6 +80,7 @@ so_scene* so_scene_create(const srt_scene_desc* d) {
   s->uv0 = dup_mem(d->tri_uv0, t2); s->uv1 = dup_mem(d->tri_uv1, t2); s->uv2 = dup_mem(d->tri_uv2, t2);
   s->tri_mat = dup_mem(d->tri_mat, (size_t)d->n_tri * 4);
   if (d->n_tri > 0 && d->tri_n0 && d->tri_n1 && d->tri_n2) { s->n0 = dup_mem(d->tri_n0, t3); s->n1 = dup_mem(d->tri_n1, t3); s->n2 = dup_mem(d->tri_n2, t3); }
+  if (d->n_tri > 0 && d->tri_tan0 && d->tri_tan1 && d->tri_tan2) { size_t t4 = (size_t)d->n_tri * 4 * 4; s->tg0 = dup_mem(d->tri_tan0, t4); s->tg1 = dup_mem(d->tri_tan1, t4); s->tg2 = dup_mem(d->tri_tan2, t4); }
   size_t s3 = (size_t)d->n_sph * 3 * 4, s1 = (size_t)d->n_sph * 4;
   s->c0 = dup_mem(d->sph_c0, s3); s->c1 = dup_mem(d->sph_c1, s3);
   s->t0 = dup_mem(d->sph_t0, s1); s->t1 = dup_mem(d->sph_t1, s1); s->r = dup_mem(d->sph_r, s1);
@@ -99,6 +101,7 @@ so_scene* so_scene_create(const srt_scene_desc* d) {
 void so_scene_destroy(so_scene* s) {
   if (!s) return;
   free(s->n0); free(s->n1); free(s->n2);
+  free(s->tg0); free(s->tg1); free(s->tg2);
   free(s->v0); free(s->v1); free(s->v2); free(s->uv0); free(s->uv1); free(s->uv2); free(s->tri_mat);
   free(s->c0); free(s->c1); free(s->t0); free(s->t1); free(s->r); free(s->sph_mat); free(s->nodes); free(s->mats);
   for (int i = 0; i < s->n_tex; i++) if (s->texs[i].kind == SRT_TEX_IMAGE && s->texs[i].data) free((void*)s->texs[i].data);
@@ -235,6 +238,16 @@ static int triangle_hit(const so_scene* s, int64_t i, const ray_t* r, float tMin
   rec->u = u; rec->v = v;
   rec->mat = s->tri_mat[i];
   triangle_tangent_basis(s, i, &rec->tangent, &rec->bitangent);
+  if (s->tg0) {  /* NOT the reference (srt.h: tri_tan0): glTF vertex tangents blended with the same weights */
+    const float *a = s->tg0 + 4 * i, *b = s->tg1 + 4 * i, *c = s->tg2 + 4 * i;
+    if (a[3] != 0.0f || b[3] != 0.0f || c[3] != 0.0f) {
+      v3 T = unit_vector(V(r0 * a[0] + r1 * b[0] + r2 * c[0], r0 * a[1] + r1 * b[1] + r2 * c[1], r0 * a[2] + r1 * b[2] + r2 * c[2]));
+      v3 Bu = unit_vector(vcross(rec->normal, T));
+      v3 Bt = V(a[3] * Bu.x, a[3] * Bu.y, a[3] * Bu.z);
+      float chk = (T.x + T.y + T.z) + (Bt.x + Bt.y + Bt.z);
+      if (chk == chk && fabsf(chk) <= 3.4e38f) { rec->tangent = T; rec->bitangent = Bt; }
+    }
+  }
   return 1;
 }
 

@@ -45,7 +45,8 @@ class SceneDesc(C.Structure):
                 ("n_nodes", C.c_int64), ("nodes", C.POINTER(BvhNode)),
                 ("n_mat", C.c_int32), ("materials", C.POINTER(Material)),
                 ("n_tex", C.c_int32), ("textures", C.POINTER(Texture)),
-                ("tri_n0", c_float_p), ("tri_n1", c_float_p), ("tri_n2", c_float_p)]
+                ("tri_n0", c_float_p), ("tri_n1", c_float_p), ("tri_n2", c_float_p),
+                ("tri_tan0", c_float_p), ("tri_tan1", c_float_p), ("tri_tan2", c_float_p)]
 
 
 class Camera(C.Structure):

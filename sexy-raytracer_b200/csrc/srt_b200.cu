@@ -606,6 +606,17 @@ srt_status srt_scene_create(srt_device* dev, const srt_scene_desc* d, srt_scene*
     }
     arena.add(vn, &s->sc.tri_vn);
   }
+  s->sc.tri_vt = nullptr;
+  std::vector<float4> vt;
+  if (d->n_tri > 0 && (d->tri_tan0 || d->tri_tan1 || d->tri_tan2)) {
+    if (!d->tri_tan0 || !d->tri_tan1 || !d->tri_tan2) { srt_scene_destroy(s); return fail(SRT_ERR_INVALID, "tri_tan0, tri_tan1, tri_tan2: all three or none"); }
+    vt.resize((size_t)d->n_tri * 3);
+    for (int64_t i = 0; i < d->n_tri; i++) {
+      const float* t[3] = {d->tri_tan0 + 4 * i, d->tri_tan1 + 4 * i, d->tri_tan2 + 4 * i};
+      for (int k = 0; k < 3; k++) vt[3 * i + k] = make_float4(t[k][0], t[k][1], t[k][2], t[k][3]);
+    }
+    arena.add(vt, &s->sc.tri_vt);
+  }
   std::vector<Sph> sphs((size_t)d->n_sph);
   for (int64_t j = 0; j < d->n_sph; j++) {
     const float *a = d->sph_c0 + 3 * j, *b = d->sph_c1 + 3 * j;

@@ -110,6 +110,7 @@ struct Scene {
   const Node*  nodes;  int n_nodes;
   const Tri*   tris;   int n_tri;
   const TriUV* tri_uv;
+  const float4* tri_vt;  // optional per-vertex tangents (xyz, handedness), 3 x float4 per triangle (srt_scene_desc::tri_tan0..2), or nullptr
   const float4* tri_vn;  // optional per-vertex normals, 3 x float4 per triangle (srt_scene_desc::tri_n0..2), or nullptr
   const Sph*   sphs;   int n_sph;
   const Mat*   mats;   int n_mat;

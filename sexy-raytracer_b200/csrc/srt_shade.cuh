@@ -64,9 +64,11 @@ __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ra
   rec.u = rec.v = 0.0f;
   rec.tangent = rec.bitangent = mk(0, 0, 0);
   const bool smooth = sc.tri_vn != nullptr;
+  const bool vtan = want_tbn && sc.tri_vt != nullptr;
+  bool have_tbn = false;
   if (want_uv || want_tbn || smooth) {
     const float4 ua = __ldg(&sc.tri_uv[i].a), ub = __ldg(&sc.tri_uv[i].b);
-    if (want_uv || smooth) {                                              // model.h:156-169
+    if (want_uv || smooth || vtan) {                                      // model.h:156-169
       V3 p = rec.p;
       float d0 = length(p - v0), d1 = length(p - v1), d2 = length(p - v2);
       float denom = (1.0f / d0) + (1.0f / d1) + (1.0f / d2);
@@ -80,8 +82,18 @@ __device__ __forceinline__ void finish_triangle(const Scene& sc, int i, const Ra
         const V3 s = unit_v<FAST>(mk(r0 * n0.x + r1 * n1.x + r2 * n2.x, r0 * n0.y + r1 * n1.y + r2 * n2.y, r0 * n0.z + r1 * n1.z + r2 * n2.z));
         if (s.x == s.x && s.y == s.y && s.z == s.z) rec.normal = rec.front_face ? s : -s;   // NaN weights (p on a vertex) keep the face normal
       }
+      if (vtan) {         // not the reference (srt.h: tri_tan0): glTF vertex tangents, blended like the normals
+        const float4 t0 = __ldg(&sc.tri_vt[3 * (size_t)i]), t1 = __ldg(&sc.tri_vt[3 * (size_t)i + 1]), t2 = __ldg(&sc.tri_vt[3 * (size_t)i + 2]);
+        if (t0.w != 0.0f || t1.w != 0.0f || t2.w != 0.0f) {
+          const V3 T = unit_v<FAST>(mk(r0 * t0.x + r1 * t1.x + r2 * t2.x, r0 * t0.y + r1 * t1.y + r2 * t2.y, r0 * t0.z + r1 * t1.z + r2 * t2.z));
+          const V3 Bu = unit_v<FAST>(cross(rec.normal, T));
+          const V3 Bt = mk(t0.w * Bu.x, t0.w * Bu.y, t0.w * Bu.z);
+          const float chk = (T.x + T.y + T.z) + (Bt.x + Bt.y + Bt.z);
+          if (chk == chk && fabsf(chk) <= 3.4e38f) { rec.tangent = T; rec.bitangent = Bt; have_tbn = true; }   // else: the per-face basis
+        }
+      }
     }
-    if (want_tbn) {                                                       // model.h:214-235
+    if (want_tbn && !have_tbn) {                                          // model.h:214-235
       V3 e0 = v1 - v0, e1 = v2 - v0;
       float du0x = ua.z - ua.x, du0y = ua.w - ua.y, du1x = ub.x - ua.x, du1y = ub.y - ua.y;
       float f = (du0x * du1y - du1x * du0y);

@@ -107,6 +107,8 @@ def scene_from_desc(d):
     s.tri_mat = arr(d.tri_mat, nt, 1, np.int32)
     if nt and d.tri_n0:
         s.tri_n0, s.tri_n1, s.tri_n2 = (arr(p, nt, 3, np.float32) for p in (d.tri_n0, d.tri_n1, d.tri_n2))
+    if nt and d.tri_tan0:
+        s.tri_tan0, s.tri_tan1, s.tri_tan2 = (arr(p, nt, 4, np.float32) for p in (d.tri_tan0, d.tri_tan1, d.tri_tan2))
     s.sph_c0, s.sph_c1 = arr(d.sph_c0, ns, 3, np.float32), arr(d.sph_c1, ns, 3, np.float32)
     s.sph_t0, s.sph_t1, s.sph_r = (arr(p, ns, 1, np.float32) for p in (d.sph_t0, d.sph_t1, d.sph_r))
     s.sph_mat = arr(d.sph_mat, ns, 1, np.int32)
@@ -149,12 +151,12 @@ def reference_scene(which, data_dir):
         L.srt_host_scene_free(h)
 
 
-def gltf_scene(path, texture_dir=None, reference_quirks=True, smooth_normals=False, sample_metallic_roughness=False):
+def gltf_scene(path, texture_dir=None, reference_quirks=True, smooth_normals=False, sample_metallic_roughness=False, vertex_tangents=False):
     """A glTF / GLB file through model::create(...)->init() + bvhNode + flatScene -> Scene (triangles only).  The last two
     options are not reference behaviour (include/srt_world.hpp: gltfOptions)."""
     L = _bind_world(lib())
     h = C.c_void_p()
-    opts = (1 if reference_quirks else 0) | (2 if smooth_normals else 0) | (4 if sample_metallic_roughness else 0)
+    opts = (1 if reference_quirks else 0) | (2 if smooth_normals else 0) | (4 if sample_metallic_roughness else 0) | (8 if vertex_tangents else 0)
     _check(L.srt_host_scene_gltf(os.fsencode(path), os.fsencode(texture_dir) if texture_dir else None, opts, C.byref(h)))
     try:
         return scene_from_desc(L.srt_host_scene_desc(h).contents)

@@ -189,6 +189,7 @@ srt_status srt_host_scene_gltf(const char* gltf_path, const char* texture_dir, i
   gltfConfig().referenceQuirks = (options & SRT_GLTF_REFERENCE_QUIRKS) != 0;
   gltfConfig().smoothNormals = (options & SRT_GLTF_SMOOTH_NORMALS) != 0;
   gltfConfig().sampleMetallicRoughness = (options & SRT_GLTF_SAMPLE_MR) != 0;
+  gltfConfig().vertexTangents = (options & SRT_GLTF_VERTEX_TANGENTS) != 0;
   hittableList objects;
   bool ok = true;
   addModel(objects, S->models, gltf_path, ok);

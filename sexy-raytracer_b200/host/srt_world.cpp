@@ -415,11 +415,28 @@ bool flatScene::build(const hittableList& world) {
       }
     }
   }
+  // vertex tangents, when any mesh has them; triangles of meshes without get w = 0 (= keep the per-face basis)
+  tri_tan0.clear(); tri_tan1.clear(); tri_tan2.clear();
+  bool any_tangents = false;
+  for (const triangle* t : soa.tris) if (!t->parentMesh.lock()->tangents.empty()) { any_tangents = true; break; }
+  if (any_tangents) {
+    std::vector<float>* T[3] = {&tri_tan0, &tri_tan1, &tri_tan2};
+    static const float none[4] = {0, 0, 0, 0};
+    for (const triangle* t : soa.tris) {
+      const auto m = t->parentMesh.lock();
+      const bool has = t->vertices[0] < m->tangents.size() && t->vertices[1] < m->tangents.size() && t->vertices[2] < m->tangents.size();
+      for (int k = 0; k < 3; k++) {
+        const float* src = has ? m->tangents[t->vertices[k]].d : none;
+        T[k]->insert(T[k]->end(), src, src + 4);
+      }
+    }
+  }
   memset(&d, 0, sizeof d);
   d.n_tri = (int64_t)tri_mat.size();
   d.tri_v0 = tri_v0.data(); d.tri_v1 = tri_v1.data(); d.tri_v2 = tri_v2.data();
   d.tri_uv0 = tri_uv0.data(); d.tri_uv1 = tri_uv1.data(); d.tri_uv2 = tri_uv2.data(); d.tri_mat = tri_mat.data();
   if (any_normals) { d.tri_n0 = tri_n0.data(); d.tri_n1 = tri_n1.data(); d.tri_n2 = tri_n2.data(); }
+  if (any_tangents) { d.tri_tan0 = tri_tan0.data(); d.tri_tan1 = tri_tan1.data(); d.tri_tan2 = tri_tan2.data(); }
   d.n_sph = (int64_t)sph_mat.size();
   d.sph_c0 = sph_c0.data(); d.sph_c1 = sph_c1.data(); d.sph_t0 = sph_t0.data(); d.sph_t1 = sph_t1.data(); d.sph_r = sph_r.data();
   d.sph_mat = sph_mat.data();
@@ -685,6 +702,22 @@ bool gltfLoad(std::string filename, shared_ptr<model> mdl) {
                 for (int r = 0; r < 3; r++) v[r] = (float)(len > 0 ? o[r] / len : o[r]);
               }
               target->normals.push_back(vec3f(v[0], v[1], v[2]));
+            }
+          } else if (name == "TANGENT" && g_gltf.vertexTangents) {        // never read by the reference (model.h:335-365)
+            if (!g.view((long)kv.second.num, 16, ptr, stride, count, acc)) return false;
+            if (acc->string("type") != "VEC4" || (long)acc->number("componentType", 5126) != 5126) continue;
+            const Mat4* xf = (!g_gltf.referenceQuirks && mesh_xf.count((long)meshIndex)) ? &mesh_xf[(long)meshIndex] : nullptr;
+            for (size_t k = 0; k < count; k++) {
+              float v[4];
+              memcpy(v, ptr + k * stride, 16);
+              if (xf) {                                                    // a direction: the upper 3x3, renormalised; w stays
+                const double x = v[0], y = v[1], z = v[2];
+                double o[3];
+                for (int r = 0; r < 3; r++) o[r] = xf->m[r] * x + xf->m[4 + r] * y + xf->m[8 + r] * z;
+                const double len = std::sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]);
+                for (int r = 0; r < 3; r++) v[r] = (float)(len > 0 ? o[r] / len : o[r]);
+              }
+              target->tangents.push_back(vec4f(v[0], v[1], v[2], v[3]));
             }
           } else if (base == "TEXCOORD") {
             if (!g_gltf.referenceQuirks && name != "TEXCOORD_0") continue;

@@ -27,7 +27,7 @@ class Scene:
               "mat_kind", "mat_tex", "mat_albedo", "mat_params",
               "tex_kind", "tex_color", "tex_evenodd", "tex_whb", "tex_missing")
     # not the reference's behaviour, absent from files that do not use them
-    OPTIONAL = ("tri_n0", "tri_n1", "tri_n2", "mat_flags")
+    OPTIONAL = ("tri_n0", "tri_n1", "tri_n2", "tri_tan0", "tri_tan1", "tri_tan2", "mat_flags")
 
     def __init__(self):
         self.tri_v0 = self.tri_v1 = self.tri_v2 = np.zeros((0, 3), _F)
@@ -48,6 +48,7 @@ class Scene:
         self.tex_missing = np.zeros(0, _I)        # 1 = image file was missing (data NULL)
         self.tex_data = {}                        # texture id -> uint8 array [h*w*bpp]
         self.tri_n0 = self.tri_n1 = self.tri_n2 = None   # per-vertex normals [n_tri,3], all three or none
+        self.tri_tan0 = self.tri_tan1 = self.tri_tan2 = None   # per-vertex tangents xyz + handedness [n_tri,4], all three or none
         self.mat_flags = None                     # [n_mat] abi.MATF_*, None = all 0
         # config
         self.camera = np.zeros(24, _F)            # srt_camera, flat
@@ -97,6 +98,9 @@ class Scene:
         if self.tri_n0 is not None:
             assert all(np.shape(x) == (self.n_tri, 3) for x in (self.tri_n0, self.tri_n1, self.tri_n2))
             d.tri_n0, d.tri_n1, d.tri_n2 = fp(self.tri_n0), fp(self.tri_n1), fp(self.tri_n2)
+        if self.tri_tan0 is not None:
+            assert all(np.shape(x) == (self.n_tri, 4) for x in (self.tri_tan0, self.tri_tan1, self.tri_tan2))
+            d.tri_tan0, d.tri_tan1, d.tri_tan2 = fp(self.tri_tan0), fp(self.tri_tan1), fp(self.tri_tan2)
         d.n_sph = self.n_sph
         d.sph_c0, d.sph_c1 = fp(self.sph_c0), fp(self.sph_c1)
         d.sph_t0, d.sph_t1, d.sph_r = fp(self.sph_t0), fp(self.sph_t1), fp(self.sph_r)

@@ -77,6 +77,29 @@ def ext_scene(scenes):
 
 
 @pytest.fixture(scope="session")
+def tan_scene(ext_scene):
+    """ext_scene plus per-vertex tangents (srt_scene_desc::tri_tan0..2, glTF TANGENT - not read by the reference): a tangent
+    field perpendicular to the vertex normals; handedness +1 / -1 by triangle, and every third triangle without tangents
+    (w = 0: it keeps calcTangentBasis' per-face basis)."""
+    import copy
+    s = copy.copy(ext_scene)
+    F = np.float32
+    out = []
+    idx = np.arange(s.n_tri)
+    w = np.where(idx % 3 == 0, 1.0, np.where(idx % 3 == 1, -1.0, 0.0)).astype(F)
+    for n in (s.tri_n0, s.tri_n1, s.tri_n2):
+        n = n.astype(np.float64)
+        axis = np.where(np.abs(n[:, 1:2]) < 0.9, np.array([[0.0, 1.0, 0.0]]), np.array([[1.0, 0.0, 0.0]]))
+        t = np.cross(axis, n)
+        t /= np.maximum(np.linalg.norm(t, axis=1, keepdims=True), 1e-30)
+        t4 = np.concatenate([t, w[:, None]], axis=1).astype(F)
+        t4[w == 0] = 0
+        out.append(t4)
+    s.tri_tan0, s.tri_tan1, s.tri_tan2 = out
+    return s
+
+
+@pytest.fixture(scope="session")
 def port():
     """The plain-C restatement (checker).  Built on demand: gcc is part of the image."""
     from oracle import refbind

@@ -291,6 +291,53 @@ def test_smooth_normals_and_packed_mr_vs_port(device, ext_scene, port):
     assert devmod.lib().srt_scene_create(device.h, ctypes.byref(d), ctypes.byref(hs)) != 0 and not hs
 
 
+def test_vertex_tangents_vs_port(device, tan_scene, port):
+    """srt_scene_desc::tri_tan0..2 (glTF TANGENT; not the reference): hit records, shading of normal-mapped materials and whole
+    frames of the CUDA path against the C port on the same inputs."""
+    import rayset
+    ds = device.upload(tan_scene)
+    h = port.from_scene(tan_scene)
+    try:
+        rays = rayset.pinhole(tan_scene, step=2)
+        want = port.trace(h, rays)
+        rays = np.concatenate([rays, rayset.secondary(want, 20000, 5)])
+        want = port.trace(h, rays)
+        got = ds.trace(rays)
+        assert (got["prim"] == want["prim"]).all()
+        tri = (want["prim"] >= 0) & (want["prim"] < tan_scene.n_tri)
+        fin = tri & np.isfinite(want["tangent"]).all(axis=1) & np.isfinite(want["bitangent"]).all(axis=1)
+        assert fin.sum() > 1000
+        assert np.abs(got["tangent"][fin] - want["tangent"][fin]).max() <= 2e-5
+        assert np.abs(got["bitangent"][fin] - want["bitangent"][fin]).max() <= 2e-5
+        sel = np.flatnonzero(fin)[::7][:5000]
+        rng = np.random.default_rng(12)
+        rv = rng.normal(size=(len(sel), 3))
+        xi = np.concatenate([rv / np.linalg.norm(rv, axis=1, keepdims=True), rng.random((len(sel), 1))], axis=1).astype(np.float32)
+        att_w, _, out_w, sc_w = port.shade_kat(h, rays[sel], want[sel], xi)
+        att_g, _, out_g, sc_g = ds.shade_kat(rays[sel], want[sel], xi)
+        assert (sc_w == sc_g).all()
+        assert (np.abs(att_g - att_w) / np.maximum(np.abs(att_w), 1e-4)).max() <= 1e-4
+        for variant in (1, 2):
+            P = tan_scene.render_params(width=213, height=120, spp=8, seed=5, variant=variant)
+            want_f, st_w = port.render(h, tan_scene, P, nthreads=8)
+            got_f, _, st = ds.render(P, want_rgba=False)
+            assert st.variant == variant and st.paths == st_w.paths
+            assert abs(int(st.segments) - int(st_w.segments)) <= 1e-3 * st_w.segments
+            fin2 = np.isfinite(want_f).all(axis=2) & np.isfinite(got_f).all(axis=2)
+            err = np.abs(got_f - want_f).max(axis=2) / np.maximum(np.abs(want_f).max(axis=2), 1e-3)
+            assert (err[fin2] > 1e-3).mean() < 0.01
+            assert abs(got_f[fin2].sum() - want_f[fin2].sum()) <= 2e-3 * want_f[fin2].sum()
+    finally:
+        port.free(h)
+        ds.close()
+    import ctypes
+    from sexy_raytracer_b200 import device as devmod
+    d = tan_scene.desc()
+    d.tri_tan2 = None                             # all three tangent arrays or none
+    hs = ctypes.c_void_p()
+    assert devmod.lib().srt_scene_create(device.h, ctypes.byref(d), ctypes.byref(hs)) != 0 and not hs
+
+
 @pytest.mark.parametrize("name", SCENES)
 def test_frame_vs_reference_image(name, dev_scenes, scenes, golden):
     """Converged-image criterion: PSNR(GPU, ref_A) >= PSNR(ref_A, ref_B) - 0.5 dB on RGBA8, and

@@ -222,3 +222,38 @@ def test_port_aabb_adversarial_vs_reference(port, ref):
     for seed in (11, 12, 13):
         rays, boxes, tmm = rayset.aabb_adversarial(300000, seed)
         assert (port.aabb_kat(rays, boxes, tmm) == ref.aabb_kat(rays, boxes, tmm)).all()
+
+
+def test_port_vertex_tangents(port, ext_scene, tan_scene):
+    """srt_scene_desc::tri_tan0..2 (glTF TANGENT, never read by the reference) in the port, against a numpy restatement:
+    tangent = unit(sum r_k t_k) with the inverse-distance weights of model.h:158-166, bitangent = w0 * unit(normal x tangent);
+    triangles whose vertices carry w = 0 keep calcTangentBasis' per-face basis bit for bit; nothing else of the record moves."""
+    rays = rayset.pinhole(ext_scene, step=3)
+    he, ht = port.from_scene(ext_scene), port.from_scene(tan_scene)
+    try:
+        a, b = port.trace(he, rays), port.trace(ht, rays)
+    finally:
+        port.free(he); port.free(ht)
+    for f in ("prim", "mat", "front_face", "t", "p", "uv", "normal"):
+        assert same_bits(a[f], b[f]), f
+    tri = (a["prim"] >= 0) & (a["prim"] < ext_scene.n_tri)
+    i = a["prim"][tri]
+    w0 = tan_scene.tri_tan0[i][:, 3]
+    keep = w0 == 0
+    assert keep.sum() > 100 and (~keep).sum() > 300
+    assert same_bits(a["tangent"][~tri], b["tangent"][~tri]) and same_bits(a["bitangent"][~tri], b["bitangent"][~tri])
+    assert same_bits(a["tangent"][tri][keep], b["tangent"][tri][keep]) and same_bits(a["bitangent"][tri][keep], b["bitangent"][tri][keep])
+    F = np.float32
+    p = a["p"][tri]
+    wt = [F(1) / np.sqrt((((p - v[i]) ** 2).astype(F)).sum(axis=1, dtype=np.float64)).astype(F) for v in (ext_scene.tri_v0, ext_scene.tri_v1, ext_scene.tri_v2)]
+    den = (wt[0] + wt[1] + wt[2]).astype(F)
+    r = [(x / den).astype(F) for x in wt]
+    T = r[0][:, None] * tan_scene.tri_tan0[i][:, :3] + r[1][:, None] * tan_scene.tri_tan1[i][:, :3] + r[2][:, None] * tan_scene.tri_tan2[i][:, :3]
+    with np.errstate(invalid="ignore", divide="ignore"):        # (rows without tangents are masked out below)
+        T = T / np.linalg.norm(T, axis=1, keepdims=True)
+        B = np.cross(b["normal"][tri].astype(np.float64), T)
+        B = w0[:, None] * B / np.linalg.norm(B, axis=1, keepdims=True)
+    use = ~keep & np.isfinite(T).all(axis=1) & np.isfinite(B).all(axis=1)
+    assert np.abs(b["tangent"][tri][use] - T[use]).max() < 2e-5
+    assert np.abs(b["bitangent"][tri][use] - B[use]).max() < 5e-5
+    assert np.abs(b["tangent"][tri][use] - a["tangent"][tri][use]).max() > 0.05        # and it is not the per-face basis

@@ -331,6 +331,37 @@ def test_example_renders_config1_like_the_library(tmp_path, device, dev_scenes, 
 
 
 # ---- progressive accumulation + checkpoint ----------------------------------------------------------
+def test_gltf_vertex_tangents_option(tmp_path):
+    """glTF TANGENT (VEC4: xyz + handedness) is read only under vertexTangents - the reference never reads it
+    (model.h:335-365) - carried through node transforms as a direction (upper 3x3, renormalised; w untouched), and lands in
+    srt_scene_desc::tri_tan0..2 per triangle vertex.  With the flag off the flattened scene is unchanged."""
+    path, pos, _ = _tiny_gltf(tmp_path, name="t")
+    doc = json.loads(open(path).read())
+    tan = np.array([[1, 0, 0, 1], [0.6, 0.8, 0, 1], [0, 1, 0, -1], [0, 0.6, 0.8, -1]], np.float32)
+    blob = base64.b64decode(doc["buffers"][0]["uri"].split(",", 1)[1])
+    off = len(blob)
+    blob += tan.tobytes()
+    doc["buffers"][0] = {"byteLength": len(blob), "uri": "data:application/octet-stream;base64," + base64.b64encode(blob).decode()}
+    doc["bufferViews"].append({"buffer": 0, "byteOffset": off, "byteLength": tan.nbytes})
+    doc["accessors"].append({"bufferView": 3, "componentType": 5126, "count": 4, "type": "VEC4"})
+    doc["meshes"][0]["primitives"][0]["attributes"]["TANGENT"] = 3
+    doc["nodes"][0]["scale"] = [2.0, 1.0, 1.0]
+    open(path, "w").write(json.dumps(doc))
+    tex_dir = str(tmp_path) + "/"
+    plain = host.gltf_scene(path, tex_dir, reference_quirks=False)
+    assert plain.tri_tan0 is None
+    s = host.gltf_scene(path, tex_dir, reference_quirks=False, vertex_tangents=True)
+    assert _same(s.tri_v0, plain.tri_v0) and _same(s.nodes, plain.nodes) and s.tri_n0 is None
+    want = tan.astype(np.float64).copy()
+    want[:, 0] *= 2.0                                                    # a direction under diag(2,1,1)
+    want[:, :3] /= np.linalg.norm(want[:, :3], axis=1, keepdims=True)
+    want = want.astype(np.float32)
+    assert np.allclose(s.tri_tan0, want[[0, 0]], atol=1e-6) and np.allclose(s.tri_tan1, want[[1, 2]], atol=1e-6)
+    assert np.allclose(s.tri_tan2, want[[2, 3]], atol=1e-6)
+    q = host.gltf_scene(path, tex_dir, reference_quirks=True, vertex_tangents=True)        # the quirks ignore node transforms
+    assert np.allclose(q.tri_tan1, tan[[1, 2]], atol=1e-7)
+
+
 def test_pfm_round_trip(tmp_path):
     """srt_pfm_write / srt_pfm_read (a raw fp32 dump for parity tooling): values bit-exact, row 0 stays the
     top row although the file stores rows bottom-up, the scale factor applies on the way out, the header is what other PFM
