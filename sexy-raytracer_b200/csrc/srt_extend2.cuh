@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_wf_extend2(Scene sc, WfPool pool
           mine = (long long)e.x; link = (int)e.y; tCur = __uint_as_float(e.z); prim = (int)e.w;
         } else if (q - take < fresh) {
           const unsigned long long idx = base + (unsigned long long)(q - take);
-          if (idx < (unsigned long long)pool.n_slots) { mine = (long long)idx; tCur = INF; prim = -1; is_fresh = true; }
+          if (idx < (unsigned long long)pool.n_slots) { mine = pool.order ? (long long)pool.order[idx] : (long long)idx; tCur = INF; prim = -1; is_fresh = true; }
         }
         if (mine >= 0) {
           const float4 d = __ldg(&pool.ray_d[mine]), o = __ldg(&pool.ray_o[mine]);
